@@ -1,0 +1,293 @@
+#!/usr/bin/env python
+"""bench.py — diffusion-head token-steps/s (BASELINE.json metric) on N B200s of one node.
+
+Workload (config.workload): BASELINE config 3, "UVA PushT-M multitask inference, 100-step DDPM + CFG
+over all masked tokens, batch 64 per GPU": DiffLoss.sample on 64 x 1024 cond rows || 64 x 1024 uncond
+rows = 131 072 rows per GPU, C=16, cfg=3.0, temperature 0.95, clip_denoised=False, 100 denoise steps.
+One bench "step" = one such sample() call = 13 107 200 row-steps per GPU.  (token-steps/s is a
+sampling metric; configs[1], the training step, is reported by --workload train as rows/s.)
+
+    python bench.py --gpus 1 --steps 3 --warmup 3
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
+        --master-port P bench.py --gpus N --steps K --warmup W
+    python bench.py --impl reference ...      # CPU arm: the oracle port of the reference head
+
+value  : whole-job row-steps/s with z / start noise / step noise already resident in HBM, timed with
+         CUDA events around K library calls (max over ranks).
+e2e    : same metric through the public API DiffLoss.sample(z) with z in pinned HOST memory: the
+         H2D copy of z, the RNG draws, the 100-step loop and the D2H copy of the samples are all timed.
+roofline: dominant kernel = the AdaLN-modulation GEMM ([rows,1024] x [1024,20480], 61% of the
+         algorithmic FLOPs), timed live with CUDA event pairs on the launch stream.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+C, Z, W, DEPTH, T_GEN = 16, 768, 1024, 6, 100
+CFG, TEMP = 3.0, 0.95
+FLOP_PER_ROW_STEP = 2 * (C * W + DEPTH * 5 * W * W + 2 * W * W + W * 2 * C)  # 67 207 168
+ADA_FLOP_PER_ROW = 2 * (3 * DEPTH + 2) * W * W  # AdaLN modulation GEMM, per row per denoise step
+TRAIN_FLOP_PER_ROW = 6 * (C * W + 256 * W + W * W + Z * W + DEPTH * 5 * W * W + 2 * W * W + W * 2 * C)
+
+
+def _peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return float(d["bf16_tflops"]), float(d.get("bf16_tflops_sustained", d["bf16_tflops"])), "measured"
+    return 1590.0, 1400.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except Exception:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def __exit__(self, *a):
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except Exception:
+                self.proc.kill()
+
+    def summary(self):
+        sm, mx, reasons = [], 0.0, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx = max(mx, float(r[1]))
+                for n, v in zip(names, r[3:7]):
+                    if v.lower().startswith("active"):
+                        reasons.add(n)
+            except Exception:
+                pass
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def make_head(dev, cls_name="DiffLoss"):
+    """Reference init (DL:237-259) then the zero-initialised tensors re-drawn N(0, 0.02), seed 0, so
+    the net is not identically zero (SURVEY §8d synthetic inputs)."""
+    import torch
+
+    from unified_video_action_b200 import DiffLoss
+
+    torch.manual_seed(0)
+    head = DiffLoss(C, Z, DEPTH, W, str(T_GEN), n_frames=4, language_emb_model=None, language_emb_model_type=None)
+    g = torch.Generator().manual_seed(0)
+    with torch.no_grad():
+        for n, p in head.named_parameters():
+            if "adaLN_modulation" in n or n.startswith("net.final_layer.linear"):
+                p.copy_(0.02 * torch.randn(p.shape, generator=g))
+    return head.to(dev)
+
+
+def cpu_sample_rate(rows, steps, seed=0):
+    """The oracle port of the reference head (fp32, torch CPU, all host threads) on `rows` rows x
+    `steps` denoise steps of the same CFG workload -> row-steps/s."""
+    import torch
+
+    from oracle import uva_oracle as O
+
+    P = O.to_torch_params(O.make_params(C, Z, W, DEPTH, seed=1))
+    S = O.create_schedule(str(T_GEN))
+    g = torch.Generator().manual_seed(seed)
+    z = torch.randn(rows, Z, generator=g)
+    half = torch.randn(rows // 2, C, generator=g)
+    x0 = torch.cat([half, half])
+    nz = torch.randn(steps, rows, C, generator=g)
+    t0 = time.perf_counter()
+    O.sample_loop(P, S, z, x0, nz, temperature=TEMP, cfg=CFG, clip_denoised=False, num_steps=steps)
+    dt = time.perf_counter() - t0
+    return rows * steps / dt, dt
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU implementation of the path (oracle port: the reference
+    is Python and cannot travel to the GPU box), all host threads, bounded sample per step."""
+    import torch
+
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cores = torch.get_num_threads()
+    rows, dsteps = 1024, 2
+    for _ in range(args.warmup):
+        cpu_sample_rate(256, 1)
+    rates, times = [], []
+    for k in range(args.steps):
+        r, dt = cpu_sample_rate(rows, dsteps, seed=k)
+        rates.append(r)
+        times.append(dt)
+    total = rows * dsteps * args.steps / sum(times)
+    sample = f"{rows} rows (512 cond || 512 uncond) x {dsteps} of the 100 denoise steps per bench step, fp32 torch CPU"
+    line = {
+        "impl": "reference", "metric": "diffusion-head token-steps/sec", "value": total, "unit": "row-steps/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * sum(times) / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "C3: DiffLoss.sample, 100-step DDPM + CFG 3.0, C=16 (bounded CPU sample)", "rows_per_step": rows,
+                   "denoise_steps_per_step": dsteps},
+        "cpu_baseline": {"value": total, "unit": "row-steps/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": total, "unit": "row-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--rows", type=int, default=131072, help="rows per GPU (cond || uncond)")
+    ap.add_argument("--denoise-steps", type=int, default=T_GEN)
+    ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+        return
+
+    import torch
+    import torch.distributed as dist
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    os.environ["UVA_B200_PRECISION"] = args.precision
+    head = make_head(dev)
+    lib_head = head.net.head()
+    rows, K, Wm, dsteps = args.rows, args.steps, max(args.warmup, 0), args.denoise_steps
+
+    g = torch.Generator(device=dev).manual_seed(1234 + rank)
+    z = torch.randn(rows, Z, generator=g, device=dev)
+    halfn = torch.randn(rows // 2, C, generator=g, device=dev)
+    x0 = torch.cat([halfn, halfn])
+    step_noise = torch.randn(dsteps, rows, C, generator=g, device=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def call():
+        return lib_head.sample(z, x0, step_noise, temperature=TEMP, cfg=CFG, clip_denoised=False, k_begin=0, k_end=dsteps)
+
+    for _ in range(Wm):
+        call()
+    barrier()
+    lib_head.timing_enable(True)
+    l0 = lib_head.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(local) as clk:
+        barrier()
+        e0.record()
+        for _ in range(K):
+            out = call()
+        e1.record()
+        barrier()
+    ms = e0.elapsed_time(e1)
+    launches = lib_head.launch_count() - l0
+    lib_head.timing_enable(False)
+    ada_ms, ada_n = lib_head.timing_read(0)
+    for cat in (1, 2, 3, 4):
+        lib_head.timing_read(cat)
+    assert torch.isfinite(out).all(), "non-finite samples"
+    t = torch.tensor([ms], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    value = world * rows * dsteps * K / (ms / 1e3)
+
+    # ---- e2e through the public API, host buffers ----
+    z_host = z.cpu().pin_memory()
+    out_host = torch.empty(rows, C, dtype=torch.float32).pin_memory()
+    z_dev = torch.empty_like(z)
+
+    def call_e2e():
+        z_dev.copy_(z_host, non_blocking=True)
+        o = head.sample(z_dev, temperature=TEMP, cfg=CFG)
+        out_host.copy_(o, non_blocking=True)
+
+    e2e = None
+    if dsteps == T_GEN:
+        call_e2e()
+        barrier()
+        e0.record()
+        for _ in range(K):
+            call_e2e()
+        e1.record()
+        barrier()
+        t = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e = {"value": world * rows * T_GEN * K / (float(t.item()) / 1e3), "unit": "row-steps/s",
+               "h2d_bytes_per_step": rows * Z * 4, "d2h_bytes_per_step": rows * C * 4}
+
+    if rank == 0:
+        burst, sustained, src = _peaks()
+        ada_tflops = (ADA_FLOP_PER_ROW * rows * dsteps * K / (ada_ms / 1e3) / 1e12) if ada_ms > 0 else None
+        line = {
+            "metric": "diffusion-head token-steps/sec", "value": value, "unit": "row-steps/s", "n_gpus": world,
+            "steps": K, "warmup": Wm, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": args.precision, "data": "synthetic",
+            "config": {"workload": "C3: DiffLoss.sample 100-step DDPM + CFG 3.0, B=64/GPU -> 131072 rows (cond||uncond), C=16",
+                       "rows_per_gpu": rows, "denoise_steps": dsteps, "cfg": CFG, "temperature": TEMP,
+                       "l2": "inputs larger than L2 (z 403 MB, step noise 839 MB per call)", "parallelism": f"rows x{world}"},
+            "e2e": e2e, "gpu_launches": int(launches),
+            "roofline": {"bound": "tensor", "achieved": ada_tflops, "peak": sustained, "unit": "TFLOP/s",
+                         "frac": (ada_tflops / sustained) if ada_tflops else None, "traffic": None,
+                         "kernel": "umma_gemm_tn_kernel<256, EPI_STORE_ACT> (AdaLN modulation GEMM)",
+                         "launches_timed": int(ada_n), "avg_launch_ms": (ada_ms / ada_n) if ada_n else None,
+                         "peak_source": f"MEASURED_PEAKS.json bf16_tflops_sustained ({src}); burst {burst}"},
+            "step_tflops": value / world * FLOP_PER_ROW_STEP / 1e12,
+            "step_frac_of_burst_peak": value / world * FLOP_PER_ROW_STEP / 1e12 / burst,
+            "clocks": clk.summary(),
+        }
+        if not args.no_cpu_baseline and world == 1:
+            crow, csteps = 512, 3
+            rate, dt = cpu_sample_rate(crow, csteps)
+            line["cpu_baseline"] = {"value": rate, "unit": "row-steps/s", "cores": torch.get_num_threads(), "kind": "port",
+                                    "sample": f"{crow} rows x {csteps} denoise steps of the same CFG workload ({dt:.1f} s), fp32 torch CPU oracle port"}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,155 @@
+/*
+ * uva_head.h — C ABI of libuva_head.so: the B200-native (sm_100a) per-token diffusion head of
+ * Unified Video Action (UVA).
+ *
+ * The reference (yuz1wan/unified_video_action) has no FFI layer for this path: its "operator
+ * API" is four Python nn.Module signatures.  Every entry point below names the reference
+ * code it replaces (paths relative to
+ * /root/reference/unified_video_action/model/autoregressive/):
+ *
+ *   DL  = diffusion_loss.py          GD = diffusion/gaussian_diffusion.py
+ *   DAL = diffusion_action_loss.py   RS = diffusion/respace.py
+ *   DI  = diffusion/__init__.py      DU = diffusion/diffusion_utils.py
+ *
+ * Conventions
+ *   - plain C types only; every `const float*` / `float*` / `void*` argument is a DEVICE pointer
+ *     unless the comment says "host"; tensors are dense row-major;
+ *   - every call enqueues work on the given cudaStream_t (passed as void*) and returns without
+ *     synchronising; the caller owns every buffer, the library owns the opaque handle (packed
+ *     weights, schedule tables, timestep-embedding table);
+ *   - return value 0 = ok, negative = error; uva_last_error() gives the message (thread local);
+ *   - there is no CPU fallback: without a CUDA device every compute entry point fails.
+ */
+#ifndef UVA_HEAD_H_
+#define UVA_HEAD_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct UvaHead UvaHead;
+
+enum {
+  UVA_OK = 0,
+  UVA_ERR_INVALID = -1,   /* bad argument / shape / alignment (checked before any launch) */
+  UVA_ERR_CUDA = -2,      /* CUDA runtime or driver error                                  */
+  UVA_ERR_STATE = -3,     /* e.g. weights not loaded                                       */
+  UVA_ERR_WORKSPACE = -4  /* workspace too small                                           */
+};
+
+enum {
+  UVA_MODE_FP32 = 0, /* fp32 FFMA GEMMs, fp32 activations (<= 1e-4 rel. vs reference fp32)   */
+  UVA_MODE_BF16 = 1  /* tcgen05/TMEM bf16 GEMMs, fp32 accumulate, fp32 residual stream + LN  */
+};
+
+/* Geometry of one head = ctor arguments of DiffLoss (DL:11-42) / DiffActLoss (DAL:12-107). */
+typedef struct {
+  int32_t C;       /* target_channels: net in = C, out = 2C (learn_sigma, DI:21-46)           */
+  int32_t Z;       /* z_channels (condition width), multiple of 64                            */
+  int32_t W;       /* width, multiple of 256                                                  */
+  int32_t depth;   /* number of ResBlocks (DL:222-229)                                        */
+  int32_t T_train; /* diffusion_steps of the training process (1000)                          */
+  int32_t T_gen;   /* num_sampling_steps: respaced length of the sampling process (100)       */
+  int32_t mode;    /* UVA_MODE_*                                                              */
+} UvaHeadDesc;
+
+/* Number of parameter tensors of SimpleMLPAdaLN in reference state_dict order (DL:222-235):
+ *   time_embed.mlp.{0,2}.{weight,bias}, cond_embed.{weight,bias}, input_proj.{weight,bias},
+ *   depth x res_blocks.i.{in_ln.weight, in_ln.bias, mlp.0.weight, mlp.0.bias, mlp.2.weight,
+ *   mlp.2.bias, adaLN_modulation.1.weight, adaLN_modulation.1.bias},
+ *   final_layer.{linear.weight, linear.bias, adaLN_modulation.1.weight, adaLN_modulation.1.bias}
+ * = 8 + 8*depth + 4. */
+int32_t uva_head_num_params(int32_t depth);
+/* Element count of parameter `index` (same order); -1 when out of range. */
+int64_t uva_head_param_numel(const UvaHeadDesc* desc, int32_t index);
+
+/* Replaces DiffLoss.__init__ / create_diffusion (DL:11-42, DI:11-47, GD:102-202, RS:12-112):
+ * builds the float64 cosine schedule tables of both processes on the host, uploads fp32 copies,
+ * allocates the packed-weight storage.  Needs a CUDA device (current device is used). */
+int uva_head_create(const UvaHeadDesc* desc, UvaHead** out);
+void uva_head_destroy(UvaHead* h);
+
+/* Host-only schedule tables (GD:157-202 after RS:65-91 respacing), float64, no device needed.
+ * which: 0 = sampling process (T_gen entries), 1 = training process (T_train entries).
+ * name : "betas", "alphas_cumprod", "alphas_cumprod_prev", "sqrt_alphas_cumprod",
+ *        "sqrt_one_minus_alphas_cumprod", "sqrt_recip_alphas_cumprod",
+ *        "sqrt_recipm1_alphas_cumprod", "posterior_variance", "posterior_log_variance_clipped",
+ *        "posterior_mean_coef1", "posterior_mean_coef2", "timestep_map" (as doubles).
+ * Writes min(cap, T) doubles to out (host); returns T or a negative error. */
+int uva_schedule_table(int32_t T_train, int32_t T_gen, int32_t which, const char* name,
+                       double* out /*host*/, int32_t cap);
+
+/* Replaces nn.Module parameter access for the head: (re)packs the fp32 parameters (device
+ * pointers, reference state_dict order, see uva_head_num_params) into the kernel operand copies
+ * (bf16 K-major + transposed copies in bf16 mode, fp32 copy in fp32 mode) and rebuilds the
+ * timestep-embedding table TimestepEmbedder(t) for t = 0..T_train-1 (DL:97-139).  Call after
+ * load_state_dict and after every optimizer step. */
+int uva_head_load_weights(UvaHead* h, const float* const* params /*host array of device ptrs*/,
+                          int32_t n_params, void* stream);
+
+/* Workspace size for `rows` rows.  what: 0 = net_forward / sample, 1 = loss fwd + bwd. */
+size_t uva_head_workspace_bytes(const UvaHead* h, int64_t rows, int32_t what);
+
+/* SimpleMLPAdaLN.forward (DL:261-283): x[N,C], t[N] (original-process timesteps 0..T_train-1),
+ * c[N,Z] -> out[N,2C] fp32. */
+int uva_head_net_forward(UvaHead* h, const float* x, const int64_t* t, const float* c, int64_t N,
+                         float* out, void* ws, size_t ws_bytes, void* stream);
+
+/* DiffLoss.sample / DiffActLoss.sample after the pre-net (DL:68-90, DAL:207-227) =
+ * p_sample_loop (GD:446-541) over p_sample (GD:395-444) / p_mean_variance (GD:260-346) with the
+ * wrapped model (RS:115-127) and optionally forward_with_cfg (DL:285-293).
+ *   z[N,Z]; x_init[N,C] start noise (for cfg != 1 rows are cond || uncond and the caller passes
+ *   cat([noise, noise]) like DL:71-72); step_noise[(k_end-k_begin),N,C]: entry j is the
+ *   randn_like drawn at loop iteration k_begin + j (timestep index T_gen-1-k);
+ *   teacher (optional, may be NULL) [(k_end-k_begin),N,C]: carried state is replaced by
+ *   teacher[j] before each step (per-step parity tests);
+ *   trace (optional, may be NULL) [(k_end-k_begin),N,C]: receives the state after each step;
+ *   runs loop iterations k_begin..k_end-1 (0..T_gen for the whole chain); out[N,C]. */
+int uva_head_sample(UvaHead* h, const float* z, const float* x_init, const float* step_noise,
+                    const float* teacher, float* trace, float temperature, float cfg_scale,
+                    int32_t clip_denoised, int32_t k_begin, int32_t k_end, int64_t N, float* out,
+                    void* ws, size_t ws_bytes, void* stream);
+
+/* DiffLoss.forward / DiffActLoss.forward after the pre-net (DL:44-66, DAL:145-166) =
+ * training_losses (GD:746-818: q_sample GD:220-236, MSE + VLB GD:713-744, DU:10-73) + masked
+ * mean.  target[N,C], z[N,Z], mask[N] or NULL (plain mean, DAL:162-164), t[N] int64 (the draw
+ * of DL:51), noise[N,C] (the draw of GD:761).  Writes loss_out[1] and, if row_loss != NULL,
+ * the per-row loss [N].  Activations needed by the backward stay in ws. */
+int uva_head_loss_fwd(UvaHead* h, const float* target, const float* z, const float* mask,
+                      const int64_t* t, const float* noise, int64_t N, float* loss_out,
+                      float* row_loss, void* ws, size_t ws_bytes, void* stream);
+
+/* Backward of uva_head_loss_fwd (autograd of DL:44-66): dloss[1] is the incoming gradient of
+ * the scalar loss.  Writes dz[N,Z]; ACCUMULATES into dparams (host array of device fp32
+ * pointers, reference order; an entry may be NULL to skip).  Must follow a loss_fwd on the same
+ * ws with the same inputs. */
+int uva_head_loss_bwd(UvaHead* h, const float* dloss, const float* target, const float* z,
+                      const float* mask, const int64_t* t, const float* noise, int64_t N,
+                      float* dz, float* const* dparams /*host array of device ptrs*/,
+                      void* ws, size_t ws_bytes, void* stream);
+
+/* Number of kernel launches this handle has enqueued so far (bench.py's gpu_launches). */
+int64_t uva_head_launch_count(const UvaHead* h);
+
+/* Optional per-kernel timing for the roofline report: while enabled, every tcgen05 GEMM launch is
+ * bracketed by CUDA events on the launch stream.  timing_read synchronises on the recorded events of
+ * one category (0 AdaLN-modulation GEMM, 1 MLP GEMM 1, 2 MLP GEMM 2, 3 final linear, 4 cond_embed),
+ * returns their summed duration and count, and forgets them. */
+int uva_head_timing_enable(UvaHead* h, int32_t enable);
+int uva_head_timing_read(UvaHead* h, int32_t category, double* total_ms, int64_t* count);
+
+/* Unit check of the tcgen05 GEMM core: D[M,N] (fp32) = A[M,K] (bf16) . B[N,K]^T (bf16) + bias.
+ * N multiple of 32, K multiple of 64. */
+int uva_gemm_bf16_selftest(const void* A, const void* B, const float* bias, float* D, int64_t M,
+                           int32_t N, int32_t K, int32_t block_n, void* stream);
+
+const char* uva_last_error(void);
+const char* uva_build_info(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* UVA_HEAD_H_ */

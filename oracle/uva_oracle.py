@@ -1,0 +1,511 @@
+"""CPU oracle: a restatement of the reference's per-token diffusion head.  TEST INFRASTRUCTURE.
+
+This file restates, op for op, the arithmetic of the reference hot path so that the CUDA
+product path (``unified_video_action_b200``) can be checked against it.  It is *not* part of
+the product: only ``tests/``, ``__graft_entry__.smoke()`` and ``bench.py``'s CPU-baseline legs
+may import it.
+
+Parity status: the reference ships no tests / golden vectors for this path, so
+the oracle is pinned against the reference code itself: ``tests/golden/make_golden.py`` imports
+the unmodified reference from ``/root/reference`` in the build container, runs it on seeded
+inputs and commits the outputs under ``tests/golden/``; ``tests/test_oracle_golden.py`` checks
+this restatement against those vectors and against the float64 known-answer constants of
+SURVEY.md §8(c).
+
+Reference files restated (paths relative to
+``/root/reference/unified_video_action/model/autoregressive/``):
+
+  DL  = diffusion_loss.py            GD = diffusion/gaussian_diffusion.py
+  DAL = diffusion_action_loss.py     RS = diffusion/respace.py
+  DI  = diffusion/__init__.py        DU = diffusion/diffusion_utils.py
+
+Arithmetic runs on torch CPU tensors (the reference is torch eager, so the same ATen ops in the
+same order give bit-identical fp32 results); schedule tables are numpy float64 exactly like the
+reference.  ``dtype=torch.float64`` gives a high-precision ground truth, and
+``emulate_bf16=True`` rounds GEMM operands to bf16 at the points where the B200 bf16 kernels do,
+so the bf16 kernels can be checked to ~1e-5 instead of only to the loose 1e-2 product tolerance.
+"""
+from __future__ import annotations
+
+import math
+from dataclasses import dataclass
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+import torch.nn.functional as F
+
+# --------------------------------------------------------------------------------------
+# Schedules (numpy float64)                                           GD:102-202, RS:12-91
+# --------------------------------------------------------------------------------------
+
+
+def cosine_betas(num_steps: int, max_beta: float = 0.999) -> np.ndarray:
+    """``get_named_beta_schedule("cosine")`` -> ``betas_for_alpha_bar``  (GD:102-145)."""
+
+    def alpha_bar(t):
+        return math.cos((t + 0.008) / 1.008 * math.pi / 2) ** 2
+
+    betas = []
+    for i in range(num_steps):
+        t1 = i / num_steps
+        t2 = (i + 1) / num_steps
+        betas.append(min(1 - alpha_bar(t2) / alpha_bar(t1), max_beta))
+    return np.array(betas, dtype=np.float64)
+
+
+def space_timesteps(num_timesteps: int, section_counts) -> List[int]:
+    """Sorted list of retained timesteps (RS:12-62).  'ddimN' strides are never used by the head."""
+    if isinstance(section_counts, str):
+        section_counts = [int(x) for x in section_counts.split(",")]
+    size_per = num_timesteps // len(section_counts)
+    extra = num_timesteps % len(section_counts)
+    start_idx = 0
+    all_steps = []
+    for i, section_count in enumerate(section_counts):
+        size = size_per + (1 if i < extra else 0)
+        if size < section_count:
+            raise ValueError(f"cannot divide section of {size} steps into {section_count}")
+        frac_stride = 1 if section_count <= 1 else (size - 1) / (section_count - 1)
+        cur_idx = 0.0
+        for _ in range(section_count):
+            all_steps.append(start_idx + round(cur_idx))
+            cur_idx += frac_stride
+        start_idx += size
+    return sorted(set(all_steps))
+
+
+@dataclass
+class Schedule:
+    """All float64 tables of ``GaussianDiffusion.__init__`` (GD:157-202) plus the respacing map."""
+
+    betas: np.ndarray
+    timestep_map: np.ndarray  # index in this (possibly respaced) process -> original timestep
+    alphas_cumprod: np.ndarray
+    alphas_cumprod_prev: np.ndarray
+    sqrt_alphas_cumprod: np.ndarray
+    sqrt_one_minus_alphas_cumprod: np.ndarray
+    sqrt_recip_alphas_cumprod: np.ndarray
+    sqrt_recipm1_alphas_cumprod: np.ndarray
+    posterior_variance: np.ndarray
+    posterior_log_variance_clipped: np.ndarray
+    posterior_mean_coef1: np.ndarray
+    posterior_mean_coef2: np.ndarray
+    log_betas: np.ndarray
+
+    @property
+    def num_timesteps(self) -> int:
+        return int(self.betas.shape[0])
+
+
+def _tables_from_betas(betas: np.ndarray, timestep_map: Sequence[int]) -> Schedule:
+    betas = np.array(betas, dtype=np.float64)
+    assert betas.ndim == 1 and (betas > 0).all() and (betas <= 1).all()
+    alphas = 1.0 - betas
+    ac = np.cumprod(alphas, axis=0)
+    ac_prev = np.append(1.0, ac[:-1])
+    post_var = betas * (1.0 - ac_prev) / (1.0 - ac)
+    post_logvar = np.log(np.append(post_var[1], post_var[1:])) if len(post_var) > 1 else np.array([])
+    return Schedule(
+        betas=betas,
+        timestep_map=np.asarray(timestep_map, dtype=np.int64),
+        alphas_cumprod=ac,
+        alphas_cumprod_prev=ac_prev,
+        sqrt_alphas_cumprod=np.sqrt(ac),
+        sqrt_one_minus_alphas_cumprod=np.sqrt(1.0 - ac),
+        sqrt_recip_alphas_cumprod=np.sqrt(1.0 / ac),
+        sqrt_recipm1_alphas_cumprod=np.sqrt(1.0 / ac - 1),
+        posterior_variance=post_var,
+        posterior_log_variance_clipped=post_logvar,
+        posterior_mean_coef1=betas * np.sqrt(ac_prev) / (1.0 - ac),
+        posterior_mean_coef2=(1.0 - ac_prev) * np.sqrt(alphas) / (1.0 - ac),
+        log_betas=np.log(betas),
+    )
+
+
+def create_schedule(timestep_respacing="", diffusion_steps: int = 1000) -> Schedule:
+    """``create_diffusion(timestep_respacing, "cosine", diffusion_steps=...)`` (DI:11-47, RS:65-91)."""
+    base_betas = cosine_betas(diffusion_steps)
+    if timestep_respacing is None or timestep_respacing == "":
+        timestep_respacing = [diffusion_steps]
+    use = set(space_timesteps(diffusion_steps, timestep_respacing))
+    base = _tables_from_betas(base_betas, list(range(diffusion_steps)))
+    last = 1.0
+    new_betas, tmap = [], []
+    for i, a in enumerate(base.alphas_cumprod):
+        if i in use:
+            new_betas.append(1 - a / last)
+            last = a
+            tmap.append(i)
+    return _tables_from_betas(np.array(new_betas), tmap)
+
+
+def _extract(arr: np.ndarray, t: torch.Tensor, shape, dtype) -> torch.Tensor:
+    """``_extract_into_tensor`` (GD:892-904): float64 gather, cast, broadcast via + zeros."""
+    res = torch.from_numpy(arr)[t]
+    res = res.float() if dtype == torch.float32 else res.to(dtype)
+    while res.dim() < len(shape):
+        res = res[..., None]
+    return res + torch.zeros(shape, dtype=res.dtype)
+
+
+# --------------------------------------------------------------------------------------
+# Parameters (reference state_dict names, DL:192-259)
+# --------------------------------------------------------------------------------------
+
+
+def param_specs(C: int, Z: int, W: int, depth: int, freq: int = 256) -> List[Tuple[str, Tuple[int, ...]]]:
+    """(name, shape) of ``SimpleMLPAdaLN`` in the reference's state_dict order (DL:222-235)."""
+    specs = [
+        ("time_embed.mlp.0.weight", (W, freq)),
+        ("time_embed.mlp.0.bias", (W,)),
+        ("time_embed.mlp.2.weight", (W, W)),
+        ("time_embed.mlp.2.bias", (W,)),
+        ("cond_embed.weight", (W, Z)),
+        ("cond_embed.bias", (W,)),
+        ("input_proj.weight", (W, C)),
+        ("input_proj.bias", (W,)),
+    ]
+    for i in range(depth):
+        p = f"res_blocks.{i}."
+        specs += [
+            (p + "in_ln.weight", (W,)),
+            (p + "in_ln.bias", (W,)),
+            (p + "mlp.0.weight", (W, W)),
+            (p + "mlp.0.bias", (W,)),
+            (p + "mlp.2.weight", (W, W)),
+            (p + "mlp.2.bias", (W,)),
+            (p + "adaLN_modulation.1.weight", (3 * W, W)),
+            (p + "adaLN_modulation.1.bias", (3 * W,)),
+        ]
+    specs += [
+        ("final_layer.linear.weight", (2 * C, W)),
+        ("final_layer.linear.bias", (2 * C,)),
+        ("final_layer.adaLN_modulation.1.weight", (2 * W, W)),
+        ("final_layer.adaLN_modulation.1.bias", (2 * W,)),
+    ]
+    return specs
+
+
+def make_params(C: int, Z: int, W: int, depth: int, seed: int) -> Dict[str, np.ndarray]:
+    """Deterministic, platform-independent non-degenerate parameters (numpy PCG64).
+
+    The reference zero-initialises every AdaLN modulation layer and the final linear (DL:250-259),
+    which makes a fresh head output exactly 0; parity on such weights is vacuous.  Here every
+    matrix is drawn U(-a, a) with the Xavier bound a = sqrt(6/(fan_in+fan_out)) (what DL:238-244
+    does for the non-zeroed layers), AdaLN / final / time-MLP matrices are N(0, 0.02), LN affine
+    is 1 + N(0, 0.1) / N(0, 0.1) and biases are N(0, 0.02), so every term of the forward matters.
+    """
+    rng = np.random.Generator(np.random.PCG64(seed))
+    out: Dict[str, np.ndarray] = {}
+    for name, shape in param_specs(C, Z, W, depth):
+        if name.endswith("in_ln.weight"):
+            a = 1.0 + 0.1 * rng.standard_normal(shape)
+        elif name.endswith("in_ln.bias"):
+            a = 0.1 * rng.standard_normal(shape)
+        elif name.endswith(".bias"):
+            a = 0.02 * rng.standard_normal(shape)
+        elif "adaLN_modulation" in name or name.startswith("final_layer.linear") or name.startswith("time_embed"):
+            a = 0.02 * rng.standard_normal(shape)
+        else:
+            bound = math.sqrt(6.0 / (shape[0] + shape[1]))
+            a = rng.uniform(-bound, bound, size=shape)
+        out[name] = a.astype(np.float32)
+    return out
+
+
+def to_torch_params(params: Dict[str, np.ndarray], dtype=torch.float32, requires_grad=False) -> Dict[str, torch.Tensor]:
+    out = {}
+    for k, v in params.items():
+        t = torch.from_numpy(np.ascontiguousarray(v)).to(dtype) if isinstance(v, np.ndarray) else v.detach().to(dtype).cpu()
+        t = t.clone()
+        t.requires_grad_(requires_grad)
+        out[k] = t
+    return out
+
+
+def depth_of(P: Dict[str, torch.Tensor]) -> int:
+    d = 0
+    while f"res_blocks.{d}.in_ln.weight" in P:
+        d += 1
+    return d
+
+
+# --------------------------------------------------------------------------------------
+# Denoiser network (DL:93-293)
+# --------------------------------------------------------------------------------------
+
+
+def _bf16r(x: torch.Tensor) -> torch.Tensor:
+    """Round to bf16 and back (models a bf16 tensor-core operand / a bf16 activation in HBM)."""
+    return x.to(torch.bfloat16).to(x.dtype)
+
+
+def _linear(x, w, b, emulate_bf16=False, round_out=False):
+    """nn.Linear (addmm).  With ``emulate_bf16`` the operands are bf16-rounded, accumulation is
+    wide, bias is added in fp32 — what the tcgen05 bf16 kernels do."""
+    if emulate_bf16:
+        y = F.linear(_bf16r(x).double(), _bf16r(w).double()).to(x.dtype) + b
+        return _bf16r(y) if round_out else y
+    return F.linear(x, w, b)
+
+
+def timestep_embedding(t: torch.Tensor, dim: int = 256, max_period: int = 10000, dtype=torch.float32) -> torch.Tensor:
+    """Sinusoidal embedding cos||sin (DL:110-134).  The reference computes it in fp32."""
+    half = dim // 2
+    freqs = torch.exp(-math.log(max_period) * torch.arange(start=0, end=half, dtype=torch.float32) / half)
+    if dtype == torch.float64:
+        freqs = freqs.double()
+        args = t[:, None].double() * freqs[None]
+    else:
+        args = t[:, None].float() * freqs[None]
+    emb = torch.cat([torch.cos(args), torch.sin(args)], dim=-1)
+    if dim % 2:
+        emb = torch.cat([emb, torch.zeros_like(emb[:, :1])], dim=-1)
+    return emb
+
+
+def time_embed(P, t, dtype=torch.float32) -> torch.Tensor:
+    """TimestepEmbedder.forward (DL:136-139): Linear(256,W) -> SiLU -> Linear(W,W)."""
+    f = timestep_embedding(t, P["time_embed.mlp.0.weight"].shape[1], dtype=dtype)
+    h = F.silu(F.linear(f, P["time_embed.mlp.0.weight"], P["time_embed.mlp.0.bias"]))
+    return F.linear(h, P["time_embed.mlp.2.weight"], P["time_embed.mlp.2.bias"])
+
+
+def net_forward(P, x, t, c, emulate_bf16: bool = False, taps: Optional[dict] = None) -> torch.Tensor:
+    """SimpleMLPAdaLN.forward (DL:261-283) with ResBlock (DL:163-167) and FinalLayer (DL:185-189).
+
+    x [N,C], t [N] (original-process timesteps, integer), c [N,Z] -> [N,2C].
+    ``taps`` (optional dict) receives named intermediates for layer-by-layer debugging.
+    """
+    dt = x.dtype
+    W = P["input_proj.weight"].shape[0]
+    eb = emulate_bf16
+    h = F.linear(x, P["input_proj.weight"], P["input_proj.bias"])  # tiny K: kept fp32 in every mode
+    temb = time_embed(P, t, dtype=dt)
+    cemb = _linear(c, P["cond_embed.weight"], P["cond_embed.bias"], eb)
+    y = temb + cemb
+    ys = F.silu(y)  # first op of every adaLN_modulation Sequential (DL:158-160, 181-183)
+    if eb:
+        ys = _bf16r(ys)
+    if taps is not None:
+        taps["cemb"], taps["temb"], taps["ysilu"], taps["x0"] = cemb, temb, ys, h
+    for i in range(depth_of(P)):
+        p = f"res_blocks.{i}."
+        # the bf16 kernels store the whole modulation (shift | scale | gate) as bf16
+        mod = _linear(ys, P[p + "adaLN_modulation.1.weight"], P[p + "adaLN_modulation.1.bias"], eb, round_out=eb)
+        shift, scale, gate = mod.chunk(3, dim=-1)
+        n = F.layer_norm(h, (W,), P[p + "in_ln.weight"], P[p + "in_ln.bias"], 1e-6)
+        a = n * (1 + scale) + shift  # modulate (DL:93-94)
+        if eb:
+            a = _bf16r(a)
+        u = F.silu(_linear(a, P[p + "mlp.0.weight"], P[p + "mlp.0.bias"], eb))
+        if eb:
+            u = _bf16r(u)
+        v = _linear(u, P[p + "mlp.2.weight"], P[p + "mlp.2.bias"], eb)
+        h = h + gate * v
+        if taps is not None:
+            taps[f"a{i}"], taps[f"u{i}"], taps[f"x{i + 1}"], taps[f"gate{i}"] = a, u, h, gate
+    mod = _linear(ys, P["final_layer.adaLN_modulation.1.weight"], P["final_layer.adaLN_modulation.1.bias"], eb, round_out=eb)
+    shift, scale = mod.chunk(2, dim=-1)
+    n = F.layer_norm(h, (W,), None, None, 1e-6)
+    a = n * (1 + scale) + shift
+    if eb:
+        a = _bf16r(a)
+    out = _linear(a, P["final_layer.linear.weight"], P["final_layer.linear.bias"], eb)
+    if taps is not None:
+        taps["af"], taps["out"] = a, out
+    return out
+
+
+def net_forward_with_cfg(P, x, t, c, cfg_scale: float, emulate_bf16: bool = False) -> torch.Tensor:
+    """SimpleMLPAdaLN.forward_with_cfg (DL:285-293): rows are cond || uncond."""
+    C = P["input_proj.weight"].shape[1]
+    half = x[: len(x) // 2]
+    combined = torch.cat([half, half], dim=0)
+    out = net_forward(P, combined, t, c, emulate_bf16)
+    eps, rest = out[:, :C], out[:, C:]
+    cond_eps, uncond_eps = torch.split(eps, len(eps) // 2, dim=0)
+    half_eps = uncond_eps + cfg_scale * (cond_eps - uncond_eps)
+    eps = torch.cat([half_eps, half_eps], dim=0)
+    return torch.cat([eps, rest], dim=1)
+
+
+# --------------------------------------------------------------------------------------
+# Diffusion math (GD:220-444, 713-818; DU:10-73)
+# --------------------------------------------------------------------------------------
+
+
+def q_sample(S: Schedule, x_start, t, noise):
+    """GD:220-236."""
+    dt = x_start.dtype
+    return (
+        _extract(S.sqrt_alphas_cumprod, t, x_start.shape, dt) * x_start
+        + _extract(S.sqrt_one_minus_alphas_cumprod, t, x_start.shape, dt) * noise
+    )
+
+
+def q_posterior_mean_variance(S: Schedule, x_start, x_t, t):
+    """GD:238-258."""
+    dt = x_t.dtype
+    mean = (
+        _extract(S.posterior_mean_coef1, t, x_t.shape, dt) * x_start
+        + _extract(S.posterior_mean_coef2, t, x_t.shape, dt) * x_t
+    )
+    return mean, _extract(S.posterior_log_variance_clipped, t, x_t.shape, dt)
+
+
+def p_mean_variance(S: Schedule, model_output, x, t, clip_denoised: bool):
+    """GD:260-346 for EPSILON / LEARNED_RANGE, given the (already wrapped) model output [N,2C]."""
+    dt = x.dtype
+    C = x.shape[1]
+    eps, var_values = torch.split(model_output, C, dim=1)
+    min_log = _extract(S.posterior_log_variance_clipped, t, x.shape, dt)
+    max_log = _extract(S.log_betas, t, x.shape, dt)
+    frac = (var_values + 1) / 2
+    log_variance = frac * max_log + (1 - frac) * min_log
+    pred_xstart = (
+        _extract(S.sqrt_recip_alphas_cumprod, t, x.shape, dt) * x
+        - _extract(S.sqrt_recipm1_alphas_cumprod, t, x.shape, dt) * eps
+    )  # GD:348-353
+    if clip_denoised:
+        pred_xstart = pred_xstart.clamp(-1, 1)
+    mean, _ = q_posterior_mean_variance(S, pred_xstart, x, t)
+    return mean, log_variance, pred_xstart
+
+
+def p_sample(S: Schedule, model_output, x, t, noise, clip_denoised: bool, temperature: float):
+    """GD:395-444 given the model output and the step noise (``randn_like(x)`` in the reference)."""
+    mean, log_variance, pred_xstart = p_mean_variance(S, model_output, x, t, clip_denoised)
+    nonzero_mask = (t != 0).to(x.dtype).view(-1, *([1] * (x.dim() - 1)))
+    sample = mean + nonzero_mask * torch.exp(0.5 * log_variance) * noise * temperature
+    return sample, pred_xstart, mean, log_variance
+
+
+def sample_loop(
+    P,
+    S: Schedule,
+    z: torch.Tensor,
+    x_init: torch.Tensor,
+    step_noise: torch.Tensor,
+    temperature: float = 1.0,
+    cfg: float = 1.0,
+    clip_denoised: bool = False,
+    emulate_bf16: bool = False,
+    trace: bool = False,
+    teacher: Optional[torch.Tensor] = None,
+    num_steps: Optional[int] = None,
+):
+    """``p_sample_loop`` (GD:446-541) as driven by ``DiffLoss.sample`` / ``DiffActLoss.sample``
+    (DL:68-90, DAL:207-227), without the hard-coded ``.cuda()`` calls.
+
+    z [N,Z]; x_init [N,C] (for cfg != 1 the caller passes cat([noise, noise]) like DL:71-72);
+    step_noise [T,N,C], entry k is the ``randn_like`` drawn at loop iteration k (timestep index
+    T-1-k).  ``teacher`` [T,N,C] (optional) replaces the carried state before every step
+    (teacher-forced per-step parity).  Returns final sample (and per-step states if ``trace``).
+    """
+    T = S.num_timesteps
+    n_run = T if num_steps is None else num_steps
+    img = x_init
+    tmap = torch.from_numpy(S.timestep_map)
+    states = []
+    with torch.no_grad():
+        for k in range(n_run):
+            i = T - 1 - k
+            if teacher is not None:
+                img = teacher[k]
+            t = torch.full((img.shape[0],), i, dtype=torch.long)
+            new_ts = tmap[t]  # _WrappedModel (RS:122-127)
+            if cfg != 1.0:
+                out = net_forward_with_cfg(P, img, new_ts, z, cfg, emulate_bf16)
+            else:
+                out = net_forward(P, img, new_ts, z, emulate_bf16)
+            img, _, _, _ = p_sample(S, out, img, t, step_noise[k], clip_denoised, temperature)
+            if trace:
+                states.append(img)
+    if trace:
+        return img, torch.stack(states)
+    return img
+
+
+def normal_kl(mean1, logvar1, mean2, logvar2):
+    """DU:10-36."""
+    return 0.5 * (-1.0 + logvar2 - logvar1 + torch.exp(logvar1 - logvar2) + ((mean1 - mean2) ** 2) * torch.exp(-logvar2))
+
+
+def approx_standard_normal_cdf(x):
+    """DU:39-44."""
+    return 0.5 * (1.0 + torch.tanh(np.sqrt(2.0 / np.pi) * (x + 0.044715 * torch.pow(x, 3))))
+
+
+def discretized_gaussian_log_likelihood(x, means, log_scales):
+    """DU:47-73."""
+    centered_x = x - means
+    inv_stdv = torch.exp(-log_scales)
+    plus_in = inv_stdv * (centered_x + 1.0 / 255.0)
+    cdf_plus = approx_standard_normal_cdf(plus_in)
+    min_in = inv_stdv * (centered_x - 1.0 / 255.0)
+    cdf_min = approx_standard_normal_cdf(min_in)
+    log_cdf_plus = torch.log(cdf_plus.clamp(min=1e-12))
+    log_one_minus_cdf_min = torch.log((1.0 - cdf_min).clamp(min=1e-12))
+    cdf_delta = cdf_plus - cdf_min
+    return torch.where(
+        x < -0.999,
+        log_cdf_plus,
+        torch.where(x > 0.999, log_one_minus_cdf_min, torch.log(cdf_delta.clamp(min=1e-12))),
+    )
+
+
+def vb_terms_bpd(S: Schedule, frozen_out, x_start, x_t, t):
+    """GD:713-744 with clip_denoised=False (GD:789-796)."""
+    true_mean, true_logvar = q_posterior_mean_variance(S, x_start, x_t, t)
+    mean, log_variance, _ = p_mean_variance(S, frozen_out, x_t, t, clip_denoised=False)
+    kl = normal_kl(true_mean, true_logvar, mean, log_variance)
+    kl = kl.mean(dim=1) / np.log(2.0)
+    nll = -discretized_gaussian_log_likelihood(x_start, means=mean, log_scales=0.5 * log_variance)
+    nll = nll.mean(dim=1) / np.log(2.0)
+    return torch.where(t == 0, nll, kl)
+
+
+def training_losses(P, S: Schedule, x_start, t, noise, c, emulate_bf16: bool = False):
+    """GD:746-818 for LossType.MSE + LEARNED_RANGE + EPSILON.  Returns dict(loss, mse, vb) [N]."""
+    C = x_start.shape[1]
+    x_t = q_sample(S, x_start, t, noise)
+    new_ts = torch.from_numpy(S.timestep_map)[t]  # identity map for the training process (RS:122-127)
+    model_output = net_forward(P, x_t, new_ts, c, emulate_bf16)
+    eps, var_values = torch.split(model_output, C, dim=1)
+    frozen_out = torch.cat([eps.detach(), var_values], dim=1)
+    vb = vb_terms_bpd(S, frozen_out, x_start, x_t, t)
+    mse = ((noise - eps) ** 2).mean(dim=1)
+    return {"loss": mse + vb, "mse": mse, "vb": vb, "x_t": x_t, "model_output": model_output}
+
+
+def diffloss_forward(P, S: Schedule, target, z, mask, t, noise, emulate_bf16: bool = False):
+    """DiffLoss.forward (DL:44-66) with the RNG draws (t at DL:51, noise at GD:761) passed in.
+    target [N,C], z [N,Z], mask [N] or None."""
+    loss = training_losses(P, S, target, t, noise, z, emulate_bf16)["loss"]
+    if mask is not None:
+        loss = (loss * mask).sum() / mask.sum()
+    return loss.mean()
+
+
+def diffactloss_forward(P, S: Schedule, target, z, t, noise, emulate_bf16: bool = False):
+    """DiffActLoss.forward after its pre-net (DAL:145-166): plain mean over rows."""
+    return training_losses(P, S, target, t, noise, z, emulate_bf16)["loss"].mean()
+
+
+# --------------------------------------------------------------------------------------
+# Work counts — used by bench.py and DESIGN.md
+# --------------------------------------------------------------------------------------
+
+
+def sampling_flops_per_row_step(C: int, W: int = 1024, depth: int = 6) -> int:
+    """Algorithmic FLOP per row-step with time_embed / cond_embed hoisted."""
+    macs = C * W + depth * (3 * W * W + 2 * W * W) + 2 * W * W + W * 2 * C
+    return 2 * macs
+
+
+def training_flops_per_row(C: int, Z: int = 768, W: int = 1024, depth: int = 6, freq: int = 256) -> int:
+    """fwd+bwd FLOP per row = 3 x 2 x MACs as executed by the reference."""
+    macs = C * W + freq * W + W * W + Z * W + depth * (5 * W * W) + 2 * W * W + W * 2 * C
+    return 6 * macs

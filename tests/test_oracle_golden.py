@@ -1,0 +1,156 @@
+"""The CPU oracle (oracle/uva_oracle.py) against the golden vectors produced by the UNMODIFIED
+reference (tests/golden/make_golden.py) and the float64 known-answer constants of SURVEY.md §8(c).
+This is what pins the oracle; the GPU parity tests then compare the CUDA path with the oracle."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import uva_oracle as O
+
+torch.set_num_threads(max(1, min(8, os.cpu_count() or 1)))
+
+
+def _load(golden_dir, name):
+    return np.load(os.path.join(golden_dir, name + ".npz"))
+
+
+def _T(a):
+    return torch.from_numpy(np.ascontiguousarray(a))
+
+
+def test_schedule_tables_bit_exact(golden_dir):
+    g = _load(golden_dir, "schedule")
+    for tag, S in (("gen", O.create_schedule("100")), ("train", O.create_schedule(""))):
+        for k in g.files:
+            if not k.startswith(tag + "."):
+                continue
+            name = k.split(".", 1)[1]
+            mine = getattr(S, name)
+            assert np.array_equal(np.asarray(mine, dtype=g[k].dtype), g[k]), (tag, name)
+
+
+def test_schedule_known_answers():
+    S = O.create_schedule("100")
+    assert list(S.timestep_map[:8]) == [0, 10, 20, 30, 40, 50, 61, 71]
+    assert list(S.timestep_map[-4:]) == [969, 979, 989, 999]
+    kat = {
+        ("betas", 0): 4.128422482196914e-05, ("betas", 1): 6.798400685055217e-04,
+        ("betas", 50): 3.417170133661673e-02, ("betas", 99): 0.9999899991985922,
+        ("alphas_cumprod", 50): 0.48449452061639064, ("alphas_cumprod", 99): 2.4287669070228034e-09,
+        ("posterior_log_variance_clipped", 0): -10.15394511055059,
+        ("posterior_log_variance_clipped", 1): -10.15394511055059,
+        ("posterior_log_variance_clipped", 50): -3.410175196467124,
+        ("posterior_log_variance_clipped", 99): -2.5288514517641907e-04,
+        ("posterior_mean_coef1", 1): 0.9427674281100751, ("posterior_mean_coef1", 99): 0.015583721365743979,
+        ("posterior_mean_coef2", 50): 0.9500863770173814,
+        ("sqrt_recip_alphas_cumprod", 99): 20291.169634711496,
+        ("sqrt_recipm1_alphas_cumprod", 0): 0.006425412771141183,
+        ("sqrt_recipm1_alphas_cumprod", 99): 20291.169610070236,
+    }
+    for (name, i), v in kat.items():
+        assert getattr(S, name)[i] == pytest.approx(v, rel=1e-13), (name, i)
+    Tr = O.create_schedule("")
+    assert Tr.betas[999] == pytest.approx(0.999, rel=1e-12)
+    assert Tr.sqrt_alphas_cumprod[500] == pytest.approx(0.7016303673935465, rel=1e-13)
+    assert Tr.sqrt_one_minus_alphas_cumprod[500] == pytest.approx(0.7125411058677225, rel=1e-13)
+    assert Tr.posterior_log_variance_clipped[0] == pytest.approx(-10.734082532465003, rel=1e-13)
+
+
+def test_param_counts():
+    n = sum(int(np.prod(s)) for _, s in O.param_specs(16, 768, 1024, 6))
+    assert n == 35749920
+    n = sum(int(np.prod(s)) for _, s in O.param_specs(2, 768, 1024, 6))
+    assert n == 35706884
+
+
+def test_small_head_forward_and_chain(golden_dir):
+    g = _load(golden_dir, "small_head")
+    P = O.to_torch_params({k[6:]: g[k] for k in g.files if k.startswith("param.")})
+    out = O.net_forward(P, _T(g["net_x"]), _T(g["net_t"]), _T(g["net_c"]))
+    np.testing.assert_allclose(out.numpy(), g["net_out"], rtol=2e-5, atol=2e-6)
+    S = O.create_schedule("100")
+    fin, states = O.sample_loop(P, S, _T(g["s_z"]), _T(g["s_x_init"]), _T(g["s_noise"]), temperature=0.9,
+                                cfg=1.0, clip_denoised=False, trace=True)
+    np.testing.assert_allclose(states.numpy(), g["s_states"], rtol=2e-4, atol=2e-5)
+    np.testing.assert_allclose(fin.numpy(), g["s_final"], rtol=2e-4, atol=2e-5)
+
+
+def test_video_head_forward(golden_dir):
+    g = _load(golden_dir, "video_head")
+    P = O.to_torch_params(O.make_params(16, 768, 1024, 6, seed=1))
+    out = O.net_forward(P, _T(g["net_x"]), _T(g["net_t"]), _T(g["net_c"]))
+    np.testing.assert_allclose(out.numpy(), g["net_out"], rtol=2e-5, atol=2e-6)
+
+
+def test_video_head_teacher_forced_steps(golden_dir):
+    """Per-step parity: feed the reference's state x_k to the oracle, compare x_{k+1}."""
+    g = _load(golden_dir, "video_head")
+    P = O.to_torch_params(O.make_params(16, 768, 1024, 6, seed=1))
+    S = O.create_schedule("100")
+    for tag, cfg in (("s1", 1.0), ("s2", 3.0)):
+        states = _T(g[tag + "_states"])
+        teacher = torch.cat([_T(g[tag + "_x_init"])[None], states[:-1]], dim=0)
+        # run all 100 steps teacher-forced in one call
+        _, tr = O.sample_loop(P, S, _T(g[tag + "_z"]), _T(g[tag + "_x_init"]), _T(g[tag + "_noise"]), temperature=0.95,
+                              cfg=cfg, clip_denoised=False, trace=True, teacher=teacher)
+        ref = states.numpy()
+        err = np.abs(tr.numpy() - ref).reshape(100, -1).max(axis=1)
+        scale = np.abs(ref).reshape(100, -1).max(axis=1)
+        assert (err <= 1e-4 * scale + 1e-6).all(), (tag, float((err / scale).max()))
+
+
+def test_action_head_chain_clip(golden_dir):
+    g = _load(golden_dir, "action_head")
+    P = O.to_torch_params(O.make_params(2, 768, 1024, 6, seed=2))
+    S = O.create_schedule("100")
+    states = _T(g["s_states"])
+    teacher = torch.cat([_T(g["s_x_init"])[None], states[:-1]], dim=0)
+    _, tr = O.sample_loop(P, S, _T(g["s_z"]), _T(g["s_x_init"]), _T(g["s_noise"]), temperature=0.95, cfg=1.0,
+                          clip_denoised=True, trace=True, teacher=teacher)
+    np.testing.assert_allclose(tr.numpy(), states.numpy(), rtol=1e-4, atol=1e-5)
+    # free-running: clip_denoised keeps the chain bounded, so the end of the chain is comparable too
+    fin = O.sample_loop(P, S, _T(g["s_z"]), _T(g["s_x_init"]), _T(g["s_noise"]), temperature=0.95, cfg=1.0,
+                        clip_denoised=True)
+    np.testing.assert_allclose(fin.numpy(), g["s_final"], rtol=1e-3, atol=1e-4)
+
+
+def test_training_loss_and_grads(golden_dir):
+    g = _load(golden_dir, "video_head")
+    P = O.to_torch_params(O.make_params(16, 768, 1024, 6, seed=1), requires_grad=True)
+    S = O.create_schedule("")
+    z = _T(g["tr_z"]).reshape(-1, 768).requires_grad_(True)
+    loss = O.diffloss_forward(P, S, _T(g["tr_target"]).reshape(-1, 16), z, _T(g["tr_mask"]).reshape(-1),
+                              _T(g["tr_t"]), _T(g["tr_noise"]))
+    loss.backward()
+    assert loss.item() == pytest.approx(float(g["tr_loss"]), rel=1e-5)
+    np.testing.assert_allclose(z.grad.numpy().reshape(g["tr_dz"].shape), g["tr_dz"], rtol=1e-3, atol=1e-7)
+    for k, p in P.items():
+        dg = g["tr_gdigest." + k]
+        f = p.grad.double().flatten()
+        mine = np.array([f.sum().item(), f.abs().sum().item(), f.norm().item()])
+        np.testing.assert_allclose(mine[1:], dg[1:], rtol=1e-4, err_msg=k)
+        np.testing.assert_allclose(f[_T(g["tr_gidx." + k])].numpy(), g["tr_gsample." + k], rtol=2e-3,
+                                   atol=1e-6 * max(1.0, float(dg[2])), err_msg=k)
+
+
+def test_t0_decoder_nll_rows(golden_dir):
+    g = _load(golden_dir, "video_head")
+    P = O.to_torch_params(O.make_params(16, 768, 1024, 6, seed=1))
+    S = O.create_schedule("")
+    with torch.no_grad():
+        terms = O.training_losses(P, S, _T(g["t0_x"]), _T(g["t0_t"]), _T(g["t0_noise"]), _T(g["t0_c"]))
+    np.testing.assert_allclose(terms["mse"].numpy(), g["t0_mse"], rtol=1e-4, atol=1e-6)
+    np.testing.assert_allclose(terms["vb"].numpy(), g["t0_vb"], rtol=1e-4, atol=1e-6)
+    np.testing.assert_allclose(terms["loss"].numpy(), g["t0_loss"], rtol=1e-4, atol=1e-6)
+
+
+def test_action_training_rows(golden_dir):
+    g = _load(golden_dir, "action_head")
+    P = O.to_torch_params(O.make_params(2, 768, 1024, 6, seed=2))
+    S = O.create_schedule("")
+    with torch.no_grad():
+        terms = O.training_losses(P, S, _T(g["tr_target"]), _T(g["tr_t"]), _T(g["tr_noise"]), _T(g["tr_z"]))
+    np.testing.assert_allclose(terms["loss"].numpy(), g["tr_rowloss"], rtol=1e-4, atol=1e-6)
+    assert terms["loss"].mean().item() == pytest.approx(float(g["tr_loss"]), rel=1e-5)

@@ -1,0 +1,283 @@
+"""ctypes binding of ``libuva_head.so`` (C ABI in ``include/uva_head.h``).
+
+PyTorch is used only as the owner of device memory and streams; every tensor crosses the
+boundary as a raw device pointer.  There is no fallback: if the library cannot be built /
+loaded, or no B200 is present, the calls raise.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import subprocess
+import threading
+from typing import Dict, List, Optional, Sequence
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_ROOT = os.path.dirname(_HERE)
+LIB_PATH = os.path.join(_HERE, "libuva_head.so")
+CSRC = os.path.join(_HERE, "csrc")
+NVCC_FLAGS = [
+    "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
+    "-Xcompiler", "-fPIC", "-shared",
+]
+
+MODE_FP32, MODE_BF16 = 0, 1
+
+
+def _sources() -> List[str]:
+    out = [os.path.join(_ROOT, "include", "uva_head.h")]
+    for f in sorted(os.listdir(CSRC)):
+        if f.endswith((".cu", ".cuh", ".hpp", ".inc")):
+            out.append(os.path.join(CSRC, f))
+    return out
+
+
+def needs_build() -> bool:
+    if not os.path.exists(LIB_PATH):
+        return True
+    t = os.path.getmtime(LIB_PATH)
+    return any(os.path.getmtime(s) > t for s in _sources())
+
+
+def build(force: bool = False, verbose: bool = False) -> str:
+    """Compile csrc/uva_head.cu for sm_100a into the in-tree libuva_head.so (nvcc cross-compiles
+    without a GPU)."""
+    if not force and not needs_build():
+        return LIB_PATH
+    nvcc = os.environ.get("NVCC", "nvcc")
+    tmp = LIB_PATH + ".tmp.%d" % os.getpid()
+    cmd = [nvcc] + NVCC_FLAGS + ["-o", tmp, os.path.join(CSRC, "uva_head.cu")]
+    if verbose:
+        cmd.insert(1, "-Xptxas=-v")
+    res = subprocess.run(cmd, capture_output=True, text=True)
+    if res.returncode != 0:
+        raise RuntimeError("nvcc failed:\n" + res.stdout + res.stderr)
+    os.replace(tmp, LIB_PATH)
+    if verbose:
+        print(res.stderr)
+    return LIB_PATH
+
+
+class _Desc(ctypes.Structure):
+    _fields_ = [(n, ctypes.c_int32) for n in ("C", "Z", "W", "depth", "T_train", "T_gen", "mode")]
+
+
+_lib = None
+_lock = threading.Lock()
+
+# every symbol include/uva_head.h declares (tests check that all of them are exported)
+SYMBOLS = [
+    "uva_head_num_params", "uva_head_param_numel", "uva_head_create", "uva_head_destroy",
+    "uva_schedule_table", "uva_head_load_weights", "uva_head_workspace_bytes", "uva_head_net_forward",
+    "uva_head_sample", "uva_head_loss_fwd", "uva_head_loss_bwd", "uva_head_launch_count",
+    "uva_gemm_bf16_selftest", "uva_last_error", "uva_build_info", "uva_head_timing_enable", "uva_head_timing_read",
+]
+
+
+def lib() -> ctypes.CDLL:
+    global _lib
+    with _lock:
+        if _lib is not None:
+            return _lib
+        if needs_build():
+            build()
+        L = ctypes.CDLL(LIB_PATH)
+        vp, i32, i64, f32 = ctypes.c_void_p, ctypes.c_int32, ctypes.c_int64, ctypes.c_float
+        L.uva_head_num_params.restype = i32
+        L.uva_head_num_params.argtypes = [i32]
+        L.uva_head_param_numel.restype = i64
+        L.uva_head_param_numel.argtypes = [ctypes.POINTER(_Desc), i32]
+        L.uva_head_create.restype = ctypes.c_int
+        L.uva_head_create.argtypes = [ctypes.POINTER(_Desc), ctypes.POINTER(vp)]
+        L.uva_head_destroy.restype = None
+        L.uva_head_destroy.argtypes = [vp]
+        L.uva_schedule_table.restype = ctypes.c_int
+        L.uva_schedule_table.argtypes = [i32, i32, i32, ctypes.c_char_p, ctypes.POINTER(ctypes.c_double), i32]
+        L.uva_head_load_weights.restype = ctypes.c_int
+        L.uva_head_load_weights.argtypes = [vp, ctypes.POINTER(vp), i32, vp]
+        L.uva_head_workspace_bytes.restype = ctypes.c_size_t
+        L.uva_head_workspace_bytes.argtypes = [vp, i64, i32]
+        L.uva_head_net_forward.restype = ctypes.c_int
+        L.uva_head_net_forward.argtypes = [vp, vp, vp, vp, i64, vp, vp, ctypes.c_size_t, vp]
+        L.uva_head_sample.restype = ctypes.c_int
+        L.uva_head_sample.argtypes = [vp, vp, vp, vp, vp, vp, f32, f32, i32, i32, i32, i64, vp, vp, ctypes.c_size_t, vp]
+        L.uva_head_loss_fwd.restype = ctypes.c_int
+        L.uva_head_loss_fwd.argtypes = [vp, vp, vp, vp, vp, vp, i64, vp, vp, vp, ctypes.c_size_t, vp]
+        L.uva_head_loss_bwd.restype = ctypes.c_int
+        L.uva_head_loss_bwd.argtypes = [vp, vp, vp, vp, vp, vp, vp, i64, vp, ctypes.POINTER(vp), vp, ctypes.c_size_t, vp]
+        L.uva_head_launch_count.restype = i64
+        L.uva_head_launch_count.argtypes = [vp]
+        L.uva_gemm_bf16_selftest.restype = ctypes.c_int
+        L.uva_gemm_bf16_selftest.argtypes = [vp, vp, vp, vp, i64, i32, i32, i32, vp]
+        L.uva_head_timing_enable.restype = ctypes.c_int
+        L.uva_head_timing_enable.argtypes = [vp, i32]
+        L.uva_head_timing_read.restype = ctypes.c_int
+        L.uva_head_timing_read.argtypes = [vp, i32, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(i64)]
+        L.uva_last_error.restype = ctypes.c_char_p
+        L.uva_build_info.restype = ctypes.c_char_p
+        _lib = L
+        return L
+
+
+def _check(rc: int, what: str) -> None:
+    if rc != 0:
+        raise RuntimeError(f"{what} failed ({rc}): {lib().uva_last_error().decode()}")
+
+
+def schedule_table(name: str, which: int, T_train: int = 1000, T_gen: int = 100):
+    """float64 schedule table computed by the library's host code (no GPU needed)."""
+    import numpy as np
+
+    buf = (ctypes.c_double * T_train)()
+    n = lib().uva_schedule_table(T_train, T_gen, which, name.encode(), buf, T_train)
+    if n < 0:
+        raise RuntimeError(lib().uva_last_error().decode())
+    return np.array(buf[:n], dtype=np.float64)
+
+
+def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _f32c(t: torch.Tensor, what: str) -> torch.Tensor:
+    if not t.is_cuda:
+        raise RuntimeError(f"{what}: expected a CUDA tensor (the B200 head has no CPU path)")
+    if t.dtype != torch.float32:
+        t = t.float()
+    return t.contiguous()
+
+
+class Head:
+    """One diffusion head on the current CUDA device (opaque ``UvaHead*`` + a cached workspace)."""
+
+    def __init__(self, C: int, Z: int, W: int, depth: int, T_train: int = 1000, T_gen: int = 100, mode: int = MODE_BF16):
+        if not torch.cuda.is_available():
+            raise RuntimeError("unified_video_action_b200 needs a CUDA (sm_100a) device; there is no CPU fallback")
+        self.desc = _Desc(C, Z, W, depth, T_train, T_gen, mode)
+        self.C, self.Z, self.W, self.depth, self.T_train, self.T_gen, self.mode = C, Z, W, depth, T_train, T_gen, mode
+        h = ctypes.c_void_p()
+        _check(lib().uva_head_create(ctypes.byref(self.desc), ctypes.byref(h)), "uva_head_create")
+        self._h = h
+        self.device = torch.device("cuda", torch.cuda.current_device())
+        self._ws: Dict[int, torch.Tensor] = {}
+        self.n_params = lib().uva_head_num_params(depth)
+
+    def __del__(self):
+        try:
+            if getattr(self, "_h", None):
+                lib().uva_head_destroy(self._h)
+                self._h = None
+        except Exception:
+            pass
+
+    # ---- plumbing -------------------------------------------------------------------------
+    def workspace(self, rows: int, what: int) -> torch.Tensor:
+        need = int(lib().uva_head_workspace_bytes(self._h, rows, what))
+        ws = self._ws.get(what)
+        if ws is None or ws.numel() < need:
+            self._ws[what] = None
+            ws = torch.empty(max(need, 1024), dtype=torch.uint8, device=self.device)
+            self._ws[what] = ws
+        return ws
+
+    def launch_count(self) -> int:
+        return int(lib().uva_head_launch_count(self._h))
+
+    def timing_enable(self, on: bool) -> None:
+        _check(lib().uva_head_timing_enable(self._h, int(on)), "uva_head_timing_enable")
+
+    def timing_read(self, category: int):
+        """(total milliseconds, launches) of one GEMM category since the last read."""
+        ms, n = ctypes.c_double(), ctypes.c_int64()
+        _check(lib().uva_head_timing_read(self._h, category, ctypes.byref(ms), ctypes.byref(n)), "uva_head_timing_read")
+        return ms.value, n.value
+
+    def load_weights(self, params: Sequence[torch.Tensor]) -> None:
+        if len(params) != self.n_params:
+            raise RuntimeError(f"expected {self.n_params} parameter tensors, got {len(params)}")
+        keep = [_f32c(p.detach(), "parameter") for p in params]
+        for i, p in enumerate(keep):
+            want = lib().uva_head_param_numel(ctypes.byref(self.desc), i)
+            if p.numel() != want:
+                raise RuntimeError(f"parameter {i}: {p.numel()} elements, expected {want}")
+        arr = (ctypes.c_void_p * len(keep))(*[p.data_ptr() for p in keep])
+        _check(lib().uva_head_load_weights(self._h, arr, len(keep), _stream()), "uva_head_load_weights")
+
+    # ---- compute --------------------------------------------------------------------------
+    def net_forward(self, x: torch.Tensor, t: torch.Tensor, c: torch.Tensor) -> torch.Tensor:
+        x, c = _f32c(x, "x"), _f32c(c, "c")
+        t = t.to(device=x.device, dtype=torch.int64).contiguous()
+        N = x.shape[0]
+        out = torch.empty(N, 2 * self.C, dtype=torch.float32, device=x.device)
+        ws = self.workspace(N, 0)
+        _check(lib().uva_head_net_forward(self._h, x.data_ptr(), t.data_ptr(), c.data_ptr(), N, out.data_ptr(),
+                                          ws.data_ptr(), ws.numel(), _stream()), "uva_head_net_forward")
+        return out
+
+    def sample(self, z, x_init, step_noise, temperature=1.0, cfg=1.0, clip_denoised=False, teacher=None,
+               trace=False, k_begin=0, k_end=None):
+        z, x_init = _f32c(z, "z"), _f32c(x_init, "x_init")
+        N = z.shape[0]
+        k_end = self.T_gen if k_end is None else k_end
+        step_noise = _f32c(step_noise, "step_noise")
+        if step_noise.shape[0] < k_end - k_begin or step_noise.shape[1:] != x_init.shape:
+            raise RuntimeError("step_noise must be [k_end-k_begin, N, C]")
+        teacher = None if teacher is None else _f32c(teacher, "teacher")
+        tr = torch.empty(k_end - k_begin, N, self.C, dtype=torch.float32, device=z.device) if trace else None
+        out = torch.empty(N, self.C, dtype=torch.float32, device=z.device)
+        if N == 0:
+            return (out, tr) if trace else out
+        ws = self.workspace(N, 0)
+        _check(lib().uva_head_sample(self._h, z.data_ptr(), x_init.data_ptr(), step_noise.data_ptr(), _ptr(teacher),
+                                     _ptr(tr), float(temperature), float(cfg), int(bool(clip_denoised)), int(k_begin),
+                                     int(k_end), N, out.data_ptr(), ws.data_ptr(), ws.numel(), _stream()),
+               "uva_head_sample")
+        return (out, tr) if trace else out
+
+    def loss_fwd(self, target, z, mask, t, noise, want_rows=False):
+        target, z, noise = _f32c(target, "target"), _f32c(z, "z"), _f32c(noise, "noise")
+        mask = None if mask is None else _f32c(mask, "mask")
+        t = t.to(device=z.device, dtype=torch.int64).contiguous()
+        N = z.shape[0]
+        loss = torch.empty(1, dtype=torch.float32, device=z.device)
+        rows = torch.empty(N, dtype=torch.float32, device=z.device) if want_rows else None
+        ws = self.workspace(N, 1)
+        _check(lib().uva_head_loss_fwd(self._h, target.data_ptr(), z.data_ptr(), _ptr(mask), t.data_ptr(),
+                                       noise.data_ptr(), N, loss.data_ptr(), _ptr(rows), ws.data_ptr(), ws.numel(),
+                                       _stream()), "uva_head_loss_fwd")
+        return (loss, rows) if want_rows else loss
+
+    def loss_bwd(self, dloss, target, z, mask, t, noise, dparams: Sequence[Optional[torch.Tensor]]):
+        target, z, noise = _f32c(target, "target"), _f32c(z, "z"), _f32c(noise, "noise")
+        mask = None if mask is None else _f32c(mask, "mask")
+        dloss = _f32c(dloss.reshape(1), "dloss")
+        t = t.to(device=z.device, dtype=torch.int64).contiguous()
+        N = z.shape[0]
+        dz = torch.empty(N, self.Z, dtype=torch.float32, device=z.device)
+        for g in dparams:
+            if g is not None and (g.dtype != torch.float32 or not g.is_contiguous() or not g.is_cuda):
+                raise RuntimeError("gradient buffers must be contiguous fp32 CUDA tensors")
+        arr = (ctypes.c_void_p * len(dparams))(*[_ptr(g) for g in dparams])
+        ws = self.workspace(N, 1)
+        _check(lib().uva_head_loss_bwd(self._h, dloss.data_ptr(), target.data_ptr(), z.data_ptr(), _ptr(mask),
+                                       t.data_ptr(), noise.data_ptr(), N, dz.data_ptr(), arr, ws.data_ptr(),
+                                       ws.numel(), _stream()), "uva_head_loss_bwd")
+        return dz
+
+
+def gemm_bf16_selftest(A: torch.Tensor, B: torch.Tensor, bias: Optional[torch.Tensor], block_n: int) -> torch.Tensor:
+    """D = A . B^T (+ bias) through the tcgen05 GEMM core; A [M,K] bf16, B [N,K] bf16."""
+    assert A.dtype == torch.bfloat16 and B.dtype == torch.bfloat16 and A.is_cuda and B.is_cuda
+    A, B = A.contiguous(), B.contiguous()
+    M, K = A.shape
+    N = B.shape[0]
+    D = torch.empty(M, N, dtype=torch.float32, device=A.device)
+    _check(lib().uva_gemm_bf16_selftest(A.data_ptr(), B.data_ptr(), _ptr(bias), D.data_ptr(), M, N, K, block_n, _stream()),
+           "uva_gemm_bf16_selftest")
+    return D

@@ -1,0 +1,275 @@
+// Row-wise / elementwise kernels of the diffusion head (HBM-bound; vectorised, one warp per row
+// where a row reduction is needed).  Reference arithmetic cited per kernel (DL = diffusion_loss.py,
+// GD = diffusion/gaussian_diffusion.py).
+#pragma once
+#include "common.cuh"
+
+namespace uva {
+
+// ------------------------------------------------------------------------------------------
+// weight packing
+// ------------------------------------------------------------------------------------------
+// dst[r, k] (bf16, rows_pad x cols) = src[r, k] (fp32, rows x cols), zero rows for r >= rows.
+__global__ void k_pack_bf16(const float* __restrict__ src, bf16* __restrict__ dst, int rows,
+                            int rows_pad, int cols) {
+  const int64_t n = (int64_t)rows_pad * cols;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int r = (int)(i / cols);
+    dst[i] = (r < rows) ? __float2bfloat16_rn(src[i]) : __float2bfloat16_rn(0.f);
+  }
+}
+// dst[k, r] (bf16, cols_pad x rows_pad... stored [cols x rows_pad]) = src[r, k]; zero for r >= rows.
+__global__ void k_pack_bf16_t(const float* __restrict__ src, bf16* __restrict__ dst, int rows,
+                              int rows_pad, int cols) {
+  __shared__ float tile[32][33];
+  const int r0 = blockIdx.y * 32, k0 = blockIdx.x * 32;
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    const int r = r0 + i, k = k0 + threadIdx.x;
+    tile[i][threadIdx.x] = (r < rows && k < cols) ? src[(int64_t)r * cols + k] : 0.f;
+  }
+  __syncthreads();
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    const int k = k0 + i, r = r0 + threadIdx.x;
+    if (k < cols && r < rows_pad) dst[(int64_t)k * rows_pad + r] = __float2bfloat16_rn(tile[threadIdx.x][i]);
+  }
+}
+
+template <typename TO>
+__global__ void k_convert(const float* __restrict__ src, TO* __restrict__ dst, int64_t n) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (int64_t)gridDim.x * blockDim.x)
+    dst[i] = from_f32<TO>(src[i]);
+}
+
+// SiLU in place on fp32 (time-embed hidden layer, DL:104-108)
+__global__ void k_silu_inplace(float* __restrict__ p, int64_t n) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const float x = p[i];
+    p[i] = x / (1.0f + expf(-x));
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// ys = SiLU(cond_embed(c) + time_embed(t))   — first op of every adaLN_modulation (DL:158-160,
+// 181-183, 271-273).  temb is the [T_train, W] table; the timestep of row r is t_rows[r] when
+// t_rows != null, else t_all.   y_out (optional, fp32) keeps y for the backward.
+// ------------------------------------------------------------------------------------------
+template <typename TA>
+__global__ void k_ysilu(const float* __restrict__ cemb, const float* __restrict__ temb,
+                        const int64_t* __restrict__ t_rows, int t_all, TA* __restrict__ ys,
+                        float* __restrict__ y_out, int64_t rows, int W) {
+  const int wq = W / 4;
+  const int64_t n = rows * wq;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r = i / wq;
+    const int j = (int)(i - r * wq) * 4;
+    const int64_t t = t_rows ? t_rows[r] : (int64_t)t_all;
+    const float4 c = *reinterpret_cast<const float4*>(cemb + r * W + j);
+    const float4 e = __ldg(reinterpret_cast<const float4*>(temb + t * W + j));
+    float y[4] = {c.x + e.x, c.y + e.y, c.z + e.z, c.w + e.w};
+    if (y_out) *reinterpret_cast<float4*>(y_out + r * W + j) = make_float4(y[0], y[1], y[2], y[3]);
+    TA o[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) o[q] = from_f32<TA>(silu_f(y[q]));
+    if constexpr (sizeof(TA) == 2) {
+      *reinterpret_cast<uint2*>(ys + r * W + j) = *reinterpret_cast<uint2*>(o);
+    } else {
+      *reinterpret_cast<float4*>(ys + r * W + j) = *reinterpret_cast<float4*>(o);
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// input_proj (DL:233, 268): h[r, :] = x[src(r), :] . Wi^T + bi,  K = C <= 16 (CUDA cores, fp32:
+// the diffusion state is never rounded to bf16).  With CFG (half > 0) the net input of row r is
+// x[r % half] (forward_with_cfg, DL:286-287).  One block = 32 rows x W columns; each thread keeps
+// the weights of 4 output columns in registers.
+// ------------------------------------------------------------------------------------------
+constexpr int IP_ROWS = 32;
+__global__ void __launch_bounds__(256)
+k_input_proj(const float* __restrict__ x, const float* __restrict__ Wi, const float* __restrict__ bi,
+             float* __restrict__ h, int64_t rows, int C, int W, int64_t half) {
+  const int64_t r0 = (int64_t)blockIdx.x * IP_ROWS;
+  for (int j0 = threadIdx.x * 4; j0 < W; j0 += blockDim.x * 4) {
+    float w[4][16];
+    float b[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      b[q] = bi[j0 + q];
+#pragma unroll
+      for (int c = 0; c < 16; ++c) w[q][c] = (c < C) ? Wi[(int64_t)(j0 + q) * C + c] : 0.f;
+    }
+    for (int rr = 0; rr < IP_ROWS; ++rr) {
+      const int64_t r = r0 + rr;
+      if (r >= rows) break;
+      const int64_t rs = (half > 0) ? (r % half) : r;
+      float acc[4] = {b[0], b[1], b[2], b[3]};
+#pragma unroll
+      for (int c = 0; c < 16; ++c) {
+        if (c < C) {
+          const float xv = __ldg(x + rs * C + c);
+#pragma unroll
+          for (int q = 0; q < 4; ++q) acc[q] = fmaf(xv, w[q][c], acc[q]);
+        }
+      }
+      *reinterpret_cast<float4*>(h + r * W + j0) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// a = LayerNorm_{eps=1e-6}(h) [* ln_w + ln_b] * (1 + scale) + shift      (modulate DL:93-94,
+// ResBlock DL:163-166, FinalLayer DL:185-188).  One warp per row, two-pass statistics in
+// registers.  NV = W / 128 float4 per lane.  shift/scale: TA, row stride ldmod.
+// Optionally stores mean / rstd (training backward).
+// ------------------------------------------------------------------------------------------
+template <typename TA, int NV>
+__global__ void __launch_bounds__(256)
+k_lnmod(const float* __restrict__ h, const float* __restrict__ ln_w, const float* __restrict__ ln_b,
+        const TA* __restrict__ shift, const TA* __restrict__ scale, int64_t ldmod,
+        TA* __restrict__ a, float* __restrict__ stats, int64_t rows) {
+  constexpr int W = NV * 128;
+  const int lane = threadIdx.x & 31;
+  const int64_t warp_global = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t warps_total = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  for (int64_t r = warp_global; r < rows; r += warps_total) {
+    float4 v[NV];
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      v[i] = *reinterpret_cast<const float4*>(h + r * W + (lane + 32 * i) * 4);
+      s += (v[i].x + v[i].y) + (v[i].z + v[i].w);
+    }
+    const float mean = warp_sum(s) * (1.0f / W);
+    float ss = 0.f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const float dx = v[i].x - mean, dy = v[i].y - mean, dz = v[i].z - mean, dw = v[i].w - mean;
+      ss += (dx * dx + dy * dy) + (dz * dz + dw * dw);
+    }
+    const float rstd = rsqrtf(warp_sum(ss) * (1.0f / W) + 1e-6f);
+    if (stats && lane == 0) {
+      stats[2 * r] = mean;
+      stats[2 * r + 1] = rstd;
+    }
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int j = (lane + 32 * i) * 4;
+      float n[4] = {(v[i].x - mean) * rstd, (v[i].y - mean) * rstd, (v[i].z - mean) * rstd,
+                    (v[i].w - mean) * rstd};
+      if (ln_w) {
+        const float4 g = __ldg(reinterpret_cast<const float4*>(ln_w + j));
+        const float4 b = __ldg(reinterpret_cast<const float4*>(ln_b + j));
+        n[0] = n[0] * g.x + b.x; n[1] = n[1] * g.y + b.y; n[2] = n[2] * g.z + b.z; n[3] = n[3] * g.w + b.w;
+      }
+      float sh[4], sc[4];
+      if constexpr (sizeof(TA) == 2) {
+        const uint2 us = *reinterpret_cast<const uint2*>(shift + r * ldmod + j);
+        const uint2 uc = *reinterpret_cast<const uint2*>(scale + r * ldmod + j);
+        const __nv_bfloat162 s0 = *reinterpret_cast<const __nv_bfloat162*>(&us.x), s1 = *reinterpret_cast<const __nv_bfloat162*>(&us.y);
+        const __nv_bfloat162 c0 = *reinterpret_cast<const __nv_bfloat162*>(&uc.x), c1 = *reinterpret_cast<const __nv_bfloat162*>(&uc.y);
+        sh[0] = __low2float(s0); sh[1] = __high2float(s0); sh[2] = __low2float(s1); sh[3] = __high2float(s1);
+        sc[0] = __low2float(c0); sc[1] = __high2float(c0); sc[2] = __low2float(c1); sc[3] = __high2float(c1);
+      } else {
+        const float4 fs = *reinterpret_cast<const float4*>(shift + r * ldmod + j);
+        const float4 fc = *reinterpret_cast<const float4*>(scale + r * ldmod + j);
+        sh[0] = fs.x; sh[1] = fs.y; sh[2] = fs.z; sh[3] = fs.w;
+        sc[0] = fc.x; sc[1] = fc.y; sc[2] = fc.z; sc[3] = fc.w;
+      }
+      TA o[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) o[q] = from_f32<TA>(n[q] * (1.0f + sc[q]) + sh[q]);
+      if constexpr (sizeof(TA) == 2) {
+        *reinterpret_cast<uint2*>(a + r * W + j) = *reinterpret_cast<uint2*>(o);
+      } else {
+        *reinterpret_cast<float4*>(a + r * W + j) = *reinterpret_cast<float4*>(o);
+      }
+    }
+  }
+}
+
+// Generic-width variant (W multiple of 32, any size; three passes through L1) for test geometries.
+template <typename TA>
+__global__ void __launch_bounds__(256)
+k_lnmod_generic(const float* __restrict__ h, const float* __restrict__ ln_w,
+                const float* __restrict__ ln_b, const TA* __restrict__ shift,
+                const TA* __restrict__ scale, int64_t ldmod, TA* __restrict__ a,
+                float* __restrict__ stats, int64_t rows, int W) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp_global = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t warps_total = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  for (int64_t r = warp_global; r < rows; r += warps_total) {
+    float s = 0.f;
+    for (int j = lane; j < W; j += 32) s += h[r * W + j];
+    const float mean = warp_sum(s) / (float)W;
+    float ss = 0.f;
+    for (int j = lane; j < W; j += 32) {
+      const float d = h[r * W + j] - mean;
+      ss += d * d;
+    }
+    const float rstd = rsqrtf(warp_sum(ss) / (float)W + 1e-6f);
+    if (stats && lane == 0) {
+      stats[2 * r] = mean;
+      stats[2 * r + 1] = rstd;
+    }
+    for (int j = lane; j < W; j += 32) {
+      float n = (h[r * W + j] - mean) * rstd;
+      if (ln_w) n = n * ln_w[j] + ln_b[j];
+      a[r * W + j] = from_f32<TA>(n * (1.0f + to_f32(scale[r * ldmod + j])) + to_f32(shift[r * ldmod + j]));
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// One DDPM ancestral step on the net output (p_mean_variance GD:260-346 for LEARNED_RANGE /
+// EPSILON, q_posterior_mean_variance GD:238-258, p_sample GD:395-444) with the CFG mix of
+// forward_with_cfg (DL:288-293) and the temperature scaling folded in.
+//   net [rows, ldn] (eps | v) and x_cur / x_next [rows, C] are chunk-local; noise is the caller's
+//   [N, C] step-noise slab.  half > 0: chunk rows are cond || uncond (half each); eps = u + s (c - u)
+//   from rows (r % half, r % half + half); chunk row r is global row g0 + r (r < half) or
+//   g0 + ghalf + (r - half).
+// ------------------------------------------------------------------------------------------
+struct StepCoef {
+  float sqrt_recip, sqrt_recipm1, coef1, coef2, min_log, max_log;
+  int nonzero;
+};
+
+__global__ void k_ddpm_step(const float* __restrict__ net, int ldn, const float* __restrict__ x_cur,
+                            const float* __restrict__ noise, float* __restrict__ x_next, int64_t rows,
+                            int C, int64_t half, int64_t g0, int64_t ghalf, float cfg,
+                            float temperature, int clip, StepCoef k) {
+  const int64_t n = rows * C;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r = i / C;
+    const int c = (int)(i - r * C);
+    float eps;
+    if (half > 0) {
+      const int64_t rc = r % half;
+      const float ce = net[rc * ldn + c];
+      const float ue = net[(rc + half) * ldn + c];
+      eps = ue + cfg * (ce - ue);
+    } else {
+      eps = net[r * ldn + c];
+    }
+    const float v = net[r * ldn + C + c];
+    const float x = x_cur[i];
+    const float frac = (v + 1.0f) / 2.0f;
+    const float logvar = frac * k.max_log + (1.0f - frac) * k.min_log;
+    float x0 = k.sqrt_recip * x - k.sqrt_recipm1 * eps;
+    if (clip) x0 = fminf(fmaxf(x0, -1.0f), 1.0f);
+    const float mean = k.coef1 * x0 + k.coef2 * x;
+    float out = mean;
+    if (k.nonzero) {
+      // noise lives in the caller's [N, C] layout: chunk-local row r -> global row
+      const int64_t gr = g0 + ((half > 0 && r >= half) ? ghalf + (r - half) : r);
+      out = mean + expf(0.5f * logvar) * noise[gr * C + c] * temperature;
+    }
+    x_next[i] = out;
+  }
+}
+
+}  // namespace uva

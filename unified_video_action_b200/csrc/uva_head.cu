@@ -1,0 +1,331 @@
+// libuva_head.so — host orchestration + C ABI (include/uva_head.h) of the B200-native UVA
+// diffusion head.  All device work is in the kernels of this directory; this file sequences
+// them on the caller's stream.  No CPU fallback exists: every compute entry point launches
+// CUDA kernels or fails.
+#include "../../include/uva_head.h"
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "common.cuh"
+#include "elementwise.cuh"
+#include "epilogue.cuh"
+#include "schedule.hpp"
+#include "sgemm.cuh"
+#include "train_kernels.cuh"
+#include "umma_gemm.cuh"
+
+using namespace uva;
+
+// ----------------------------------------------------------------------------------------------
+// errors
+// ----------------------------------------------------------------------------------------------
+static thread_local char g_err[512] = "";
+static int fail(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+#define CUDA_TRY(expr)                                                                          \
+  do {                                                                                          \
+    cudaError_t _e = (expr);                                                                    \
+    if (_e != cudaSuccess)                                                                      \
+      return fail(UVA_ERR_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, \
+                  __LINE__);                                                                    \
+  } while (0)
+#define UVA_TRY(expr)          \
+  do {                         \
+    int _r = (expr);           \
+    if (_r != UVA_OK) return _r; \
+  } while (0)
+
+extern "C" const char* uva_last_error(void) { return g_err; }
+extern "C" const char* uva_build_info(void) {
+  return "libuva_head sm_100a (tcgen05/TMEM/TMA bf16 GEMM core + fp32 FFMA mode), built " __DATE__;
+}
+
+// ----------------------------------------------------------------------------------------------
+// parameter table (reference state_dict order, DL:222-235)
+// ----------------------------------------------------------------------------------------------
+enum { P_TE0_W = 0, P_TE0_B, P_TE2_W, P_TE2_B, P_COND_W, P_COND_B, P_INP_W, P_INP_B, P_BLOCK0 };
+enum { B_LN_W = 0, B_LN_B, B_W1, B_B1, B_W2, B_B2, B_ADA_W, B_ADA_B, B_COUNT };
+enum { F_LIN_W = 0, F_LIN_B, F_ADA_W, F_ADA_B, F_COUNT };
+static const int kFreq = 256;  // frequency_embedding_size (DL:103)
+
+extern "C" int32_t uva_head_num_params(int32_t depth) { return P_BLOCK0 + B_COUNT * depth + F_COUNT; }
+
+static void param_shape(const UvaHeadDesc& d, int idx, int64_t& rows, int64_t& cols) {
+  const int64_t W = d.W, C = d.C, Z = d.Z;
+  rows = cols = 0;
+  if (idx < P_BLOCK0) {
+    switch (idx) {
+      case P_TE0_W: rows = W; cols = kFreq; break;
+      case P_TE0_B: rows = 1; cols = W; break;
+      case P_TE2_W: rows = W; cols = W; break;
+      case P_TE2_B: rows = 1; cols = W; break;
+      case P_COND_W: rows = W; cols = Z; break;
+      case P_COND_B: rows = 1; cols = W; break;
+      case P_INP_W: rows = W; cols = C; break;
+      case P_INP_B: rows = 1; cols = W; break;
+    }
+    return;
+  }
+  const int fbase = P_BLOCK0 + B_COUNT * d.depth;
+  if (idx < fbase) {
+    switch ((idx - P_BLOCK0) % B_COUNT) {
+      case B_LN_W: case B_LN_B: case B_B1: case B_B2: rows = 1; cols = W; break;
+      case B_W1: case B_W2: rows = W; cols = W; break;
+      case B_ADA_W: rows = 3 * W; cols = W; break;
+      case B_ADA_B: rows = 1; cols = 3 * W; break;
+    }
+    return;
+  }
+  switch (idx - fbase) {
+    case F_LIN_W: rows = 2 * C; cols = W; break;
+    case F_LIN_B: rows = 1; cols = 2 * C; break;
+    case F_ADA_W: rows = 2 * W; cols = W; break;
+    case F_ADA_B: rows = 1; cols = 2 * W; break;
+  }
+}
+
+extern "C" int64_t uva_head_param_numel(const UvaHeadDesc* d, int32_t idx) {
+  if (!d || idx < 0 || idx >= uva_head_num_params(d->depth)) return -1;
+  int64_t r, c;
+  param_shape(*d, idx, r, c);
+  return r * c;
+}
+
+extern "C" int uva_schedule_table(int32_t T_train, int32_t T_gen, int32_t which, const char* name,
+                                  double* out, int32_t cap) {
+  if (T_train <= 1 || T_gen <= 0 || T_gen > T_train || !name || !out)
+    return fail(UVA_ERR_INVALID, "uva_schedule_table: bad arguments");
+  const ScheduleTables S = create_schedule(T_train, which == 0 ? T_gen : T_train);
+  const std::string n(name);
+  const int T = S.T();
+  if (n == "timestep_map") {
+    for (int i = 0; i < T && i < cap; ++i) out[i] = (double)S.timestep_map[i];
+    return T;
+  }
+  const std::vector<double>* v = S.by_name(n);
+  if (!v) return fail(UVA_ERR_INVALID, "uva_schedule_table: unknown table '%s'", name);
+  for (int i = 0; i < T && i < cap; ++i) out[i] = (*v)[i];
+  return T;
+}
+
+// ----------------------------------------------------------------------------------------------
+// handle
+// ----------------------------------------------------------------------------------------------
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
+                                    CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                    CUtensorMapFloatOOBfill);
+
+struct DevTables {  // fp32 device copies of one process' tables, [T] each
+  float *sqrt_ac = nullptr, *sqrt_1mac = nullptr, *sqrt_recip = nullptr, *sqrt_recipm1 = nullptr,
+        *coef1 = nullptr, *coef2 = nullptr, *post_logvar = nullptr, *log_beta = nullptr;
+};
+
+struct UvaHead {
+  UvaHeadDesc d;
+  int num_sms = 148;
+  int64_t chunk_rows = 32768;
+  int nmod = 0;  // (3*depth + 2) * W : width of the concatenated AdaLN modulation output
+  ScheduleTables gen, train;
+  DevTables dtrain;
+  float* d_tables = nullptr;  // backing store of dtrain
+  float* feat = nullptr;      // [T_train, 256] sinusoidal features (DL:110-134)
+  float* temb = nullptr;      // [T_train, W] TimestepEmbedder(t) table
+  float* temb_hidden = nullptr;  // [T_train, W] SiLU(Linear0(feat)) (kept for the backward)
+  // fp32 parameter copy, own layout (offsets in floats)
+  float* wf = nullptr;
+  size_t wf_floats = 0;
+  size_t o_te0w, o_te0b, o_te2w, o_te2b, o_condw, o_condb, o_inpw, o_inpb, o_adaw, o_adab, o_linw, o_linb;
+  std::vector<size_t> o_lnw, o_lnb, o_w1, o_b1, o_w2, o_b2;
+  // bf16 operand copies (bf16 mode)
+  bf16* wb = nullptr;
+  size_t wb_elems = 0;
+  size_t ob_condw, ob_adaw, ob_linw;      // [W,Z], [nmod,W], [32,W] (zero padded)
+  std::vector<size_t> ob_w1, ob_w2;       // [W,W]
+  // transposed bf16 copies for dgrad: W^T stored [K_in, N_out]
+  size_t ob_condw_t, ob_adaw_t, ob_linw_t;  // [Z,W], [W,nmod], [W,32]
+  std::vector<size_t> ob_w1_t, ob_w2_t;
+  bool weights_loaded = false;
+  int64_t launches = 0;
+  PFN_encodeTiled encode = nullptr;
+  // optional per-category GEMM timing (bench.py roofline): CUDA event pairs on the launch stream
+  bool timing = false;
+  int cur_cat = 0;
+  struct TimedLaunch { int cat; cudaEvent_t a, b; };
+  std::vector<TimedLaunch> timed;
+};
+enum { CAT_ADA = 0, CAT_MLP1, CAT_MLP2, CAT_FINAL, CAT_COND, CAT_OTHER, CAT_COUNT };
+
+#define LAUNCH_CHECK(h)                                                                       \
+  do {                                                                                        \
+    (h)->launches++;                                                                          \
+    cudaError_t _e = cudaGetLastError();                                                      \
+    if (_e != cudaSuccess)                                                                    \
+      return fail(UVA_ERR_CUDA, "kernel launch failed: %s (%s:%d)", cudaGetErrorString(_e),   \
+                  __FILE__, __LINE__);                                                        \
+  } while (0)
+
+static inline int grid_for(int64_t n, int threads, int sms) {
+  int64_t b = (n + threads - 1) / threads;
+  const int64_t cap = (int64_t)sms * 16;
+  if (b > cap) b = cap;
+  if (b < 1) b = 1;
+  return (int)b;
+}
+
+extern "C" int64_t uva_head_launch_count(const UvaHead* h) { return h ? h->launches : 0; }
+
+extern "C" int uva_head_timing_enable(UvaHead* h, int32_t enable) {
+  if (!h) return fail(UVA_ERR_INVALID, "timing_enable: null handle");
+  h->timing = enable != 0;
+  return UVA_OK;
+}
+
+extern "C" int uva_head_timing_read(UvaHead* h, int32_t category, double* total_ms, int64_t* count) {
+  if (!h || !total_ms || !count) return fail(UVA_ERR_INVALID, "timing_read: null argument");
+  double ms = 0.0;
+  int64_t n = 0;
+  std::vector<UvaHead::TimedLaunch> keep;
+  for (auto& t : h->timed) {
+    if (t.cat != category) { keep.push_back(t); continue; }
+    CUDA_TRY(cudaEventSynchronize(t.b));
+    float e = 0.f;
+    CUDA_TRY(cudaEventElapsedTime(&e, t.a, t.b));
+    ms += e;
+    n++;
+    cudaEventDestroy(t.a);
+    cudaEventDestroy(t.b);
+  }
+  h->timed.swap(keep);
+  *total_ms = ms;
+  *count = n;
+  return UVA_OK;
+}
+
+static int upload_tables(const ScheduleTables& S, DevTables& dt, float** backing) {
+  const int T = S.T();
+  std::vector<float> host((size_t)8 * T);
+  const std::vector<double>* src[8] = {&S.sqrt_alphas_cumprod, &S.sqrt_one_minus_alphas_cumprod,
+                                       &S.sqrt_recip_alphas_cumprod, &S.sqrt_recipm1_alphas_cumprod,
+                                       &S.posterior_mean_coef1, &S.posterior_mean_coef2,
+                                       &S.posterior_log_variance_clipped, &S.log_betas};
+  for (int k = 0; k < 8; ++k)
+    for (int i = 0; i < T; ++i) host[(size_t)k * T + i] = (float)(*src[k])[i];  // .float() of GD:901
+  CUDA_TRY(cudaMalloc(backing, host.size() * sizeof(float)));
+  CUDA_TRY(cudaMemcpy(*backing, host.data(), host.size() * sizeof(float), cudaMemcpyHostToDevice));
+  float* b = *backing;
+  dt.sqrt_ac = b; dt.sqrt_1mac = b + T; dt.sqrt_recip = b + 2 * T; dt.sqrt_recipm1 = b + 3 * T;
+  dt.coef1 = b + 4 * T; dt.coef2 = b + 5 * T; dt.post_logvar = b + 6 * T; dt.log_beta = b + 7 * T;
+  return UVA_OK;
+}
+
+extern "C" int uva_head_create(const UvaHeadDesc* desc, UvaHead** out) {
+  if (!desc || !out) return fail(UVA_ERR_INVALID, "uva_head_create: null argument");
+  const UvaHeadDesc& d = *desc;
+  if (d.C < 1 || d.C > 16) return fail(UVA_ERR_INVALID, "target_channels C=%d unsupported (1..16)", d.C);
+  if (d.depth < 1 || d.depth > 64) return fail(UVA_ERR_INVALID, "depth=%d unsupported", d.depth);
+  if (d.W < 32 || d.W % 32 != 0 || d.Z < 4 || d.Z % 4 != 0)
+    return fail(UVA_ERR_INVALID, "width W=%d must be a multiple of 32, Z=%d a multiple of 4", d.W, d.Z);
+  if (d.mode == UVA_MODE_BF16 && (d.W % 256 != 0 || d.Z % 64 != 0))
+    return fail(UVA_ERR_INVALID, "bf16 mode needs W %% 256 == 0 and Z %% 64 == 0 (W=%d, Z=%d)", d.W, d.Z);
+  if (d.mode != UVA_MODE_BF16 && d.mode != UVA_MODE_FP32) return fail(UVA_ERR_INVALID, "bad mode %d", d.mode);
+  if (d.T_train < 2 || d.T_gen < 1 || d.T_gen > d.T_train)
+    return fail(UVA_ERR_INVALID, "bad diffusion lengths T_train=%d T_gen=%d", d.T_train, d.T_gen);
+  int dev = 0;
+  CUDA_TRY(cudaGetDevice(&dev));
+  cudaDeviceProp prop;
+  CUDA_TRY(cudaGetDeviceProperties(&prop, dev));
+  if (prop.major != 10)
+    return fail(UVA_ERR_CUDA, "libuva_head is built for sm_100a only; device is sm_%d%d", prop.major, prop.minor);
+
+  UvaHead* h = new UvaHead();
+  h->d = d;
+  h->num_sms = prop.multiProcessorCount;
+  h->nmod = (3 * d.depth + 2) * d.W;
+  if (const char* e = getenv("UVA_CHUNK_ROWS")) {
+    long v = atol(e);
+    if (v >= 256) h->chunk_rows = (v / 256) * 256;
+  }
+  h->gen = create_schedule(d.T_train, d.T_gen);
+  h->train = create_schedule(d.T_train, d.T_train);
+  int rc = upload_tables(h->train, h->dtrain, &h->d_tables);
+  if (rc != UVA_OK) { delete h; return rc; }
+
+  // sinusoidal features for t = 0..T_train-1 (DL:110-134): cos || sin of t * freqs (fp32 args)
+  {
+    const int half = kFreq / 2;
+    std::vector<float> f((size_t)d.T_train * kFreq);
+    const float c = (float)(-std::log(10000.0));
+    for (int t = 0; t < d.T_train; ++t)
+      for (int i = 0; i < half; ++i) {
+        const float fr = expf((c * (float)i) / (float)half);
+        const float arg = (float)t * fr;
+        f[(size_t)t * kFreq + i] = (float)std::cos((double)arg);
+        f[(size_t)t * kFreq + half + i] = (float)std::sin((double)arg);
+      }
+    CUDA_TRY(cudaMalloc(&h->feat, f.size() * sizeof(float)));
+    CUDA_TRY(cudaMemcpy(h->feat, f.data(), f.size() * sizeof(float), cudaMemcpyHostToDevice));
+    CUDA_TRY(cudaMalloc(&h->temb, (size_t)d.T_train * d.W * sizeof(float)));
+    CUDA_TRY(cudaMalloc(&h->temb_hidden, (size_t)d.T_train * d.W * sizeof(float)));
+  }
+
+  // fp32 parameter layout
+  {
+    const size_t W = d.W, C = d.C, Z = d.Z;
+    size_t o = 0;
+    auto take = [&](size_t n) { size_t r = o; o += (n + 63) / 64 * 64; return r; };
+    h->o_te0w = take(W * kFreq); h->o_te0b = take(W); h->o_te2w = take(W * W); h->o_te2b = take(W);
+    h->o_condw = take(W * Z); h->o_condb = take(W); h->o_inpw = take(W * C); h->o_inpb = take(W);
+    for (int b = 0; b < d.depth; ++b) {
+      h->o_lnw.push_back(take(W)); h->o_lnb.push_back(take(W));
+      h->o_w1.push_back(take(W * W)); h->o_b1.push_back(take(W));
+      h->o_w2.push_back(take(W * W)); h->o_b2.push_back(take(W));
+    }
+    h->o_adaw = take((size_t)h->nmod * W); h->o_adab = take(h->nmod);
+    h->o_linw = take(2 * C * W); h->o_linb = take(64);
+    h->wf_floats = o;
+    CUDA_TRY(cudaMalloc(&h->wf, o * sizeof(float)));
+    CUDA_TRY(cudaMemset(h->wf, 0, o * sizeof(float)));
+  }
+  if (d.mode == UVA_MODE_BF16) {
+    const size_t W = d.W, Z = d.Z;
+    size_t o = 0;
+    auto take = [&](size_t n) { size_t r = o; o += (n + 511) / 512 * 512; return r; };
+    h->ob_condw = take(W * Z); h->ob_adaw = take((size_t)h->nmod * W); h->ob_linw = take(32 * W);
+    h->ob_condw_t = take(Z * W); h->ob_adaw_t = take((size_t)W * h->nmod); h->ob_linw_t = take(W * 32);
+    for (int b = 0; b < d.depth; ++b) {
+      h->ob_w1.push_back(take(W * W)); h->ob_w2.push_back(take(W * W));
+      h->ob_w1_t.push_back(take(W * W)); h->ob_w2_t.push_back(take(W * W));
+    }
+    h->wb_elems = o;
+    CUDA_TRY(cudaMalloc(&h->wb, o * sizeof(bf16)));
+    CUDA_TRY(cudaMemset(h->wb, 0, o * sizeof(bf16)));
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    CUDA_TRY(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres));
+    if (!fn || qres != cudaDriverEntryPointSuccess) { delete h; return fail(UVA_ERR_CUDA, "cuTensorMapEncodeTiled not available"); }
+    h->encode = (PFN_encodeTiled)fn;
+  }
+  *out = h;
+  return UVA_OK;
+}
+
+extern "C" void uva_head_destroy(UvaHead* h) {
+  if (!h) return;
+  cudaFree(h->d_tables); cudaFree(h->feat); cudaFree(h->temb); cudaFree(h->temb_hidden);
+  cudaFree(h->wf); cudaFree(h->wb);
+  delete h;
+}
+
+#include "head_infer.inc"
+#include "head_train.inc"

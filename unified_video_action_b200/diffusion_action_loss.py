@@ -1,0 +1,112 @@
+"""Drop-in ``DiffActLoss`` (action / proprioception head) backed by libuva_head.so.
+
+Mirrors the reference class (diffusion_action_loss.py, "DAL"): constructor DAL:12-107,
+``forward(target, z, task_mode, text_latents)`` DAL:109-166, ``sample(z, temperature, cfg,
+text_latents)`` DAL:168-232.  The pre-net that pools ``z [B,1024,Z]`` to ``[B,16,Z]`` runs once
+per call and stays PyTorch (cuDNN / cuBLAS) with the reference's parameter names; the denoiser,
+the loss and the 100-step loop run in the CUDA library.
+"""
+from __future__ import annotations
+
+import torch
+import torch.nn as nn
+
+from .diffusion_loss import SimpleMLPAdaLN, _FusedLoss, _require_cuda, sample_rows
+
+
+class DiffActLoss(nn.Module):
+    """Diffusion Loss for action chunks."""
+
+    def __init__(self, target_channels, z_channels, depth, width, num_sampling_steps, grad_checkpointing=False,
+                 n_frames=4, act_diff_training_steps=1000, act_diff_testing_steps="100", act_model_type="conv_fc",
+                 **kwargs):
+        super().__init__()
+        self.in_channels = target_channels
+        self.n_frames = n_frames
+        self.language_emb_model = kwargs["language_emb_model"]
+        self.language_emb_model_type = kwargs["language_emb_model_type"]
+        self.act_model_type = act_model_type
+        if int(act_diff_training_steps) != 1000:
+            # the sampling process is always respaced from 1000 steps (DAL:104-106)
+            raise NotImplementedError("the B200 head supports act_diff_training_steps=1000 (all shipped configs)")
+
+        if act_model_type == "conv_fc":  # DAL:35-61
+            self.w = 16
+            self.h = 16
+            self.num_frames = 4
+            self.num_actions = 16
+            self.conv = nn.Sequential(
+                nn.Conv2d(z_channels, z_channels, kernel_size=3, stride=1, padding=1),
+                nn.ReLU(),
+                nn.AdaptiveAvgPool2d((4, 4)),
+            )
+            self.fc = nn.Sequential(
+                nn.Linear(z_channels * 4 * 4, z_channels), nn.ReLU(), nn.Linear(z_channels, z_channels)
+            )
+            self.interpolate = nn.Linear(self.num_frames, self.num_actions)
+            self.refine = nn.Sequential(nn.Linear(z_channels, z_channels), nn.ReLU(), nn.Linear(z_channels, z_channels))
+        elif act_model_type == "conv_ori":  # DAL:63-72
+            self.w = 16
+            self.h = 16
+            self.conv_transpose3d = nn.ConvTranspose3d(z_channels, z_channels, kernel_size=(4, 1, 1), stride=(4, 1, 1))
+            self.avg_pool = nn.AvgPool3d(kernel_size=(1, self.w, self.h))
+        elif act_model_type == "conv2":  # DAL:74-79
+            self.conv = nn.Sequential(
+                nn.Conv1d(1024, 256, kernel_size=7, padding=3), nn.ReLU(), nn.Conv1d(256, 16, kernel_size=7, padding=3)
+            )
+        elif act_model_type == "fc2":  # DAL:81-86
+            self.fc = nn.Sequential(nn.Linear(1024, 256), nn.ReLU(), nn.Linear(256, 16))
+        else:
+            raise NotImplementedError
+
+        self.num_timesteps = int(act_diff_training_steps)
+        self.num_sampling_steps = int(act_diff_testing_steps)
+        self.net = SimpleMLPAdaLN(
+            in_channels=target_channels, model_channels=width, out_channels=target_channels * 2,
+            z_channels=z_channels, num_res_blocks=depth, grad_checkpointing=grad_checkpointing,
+            precision=kwargs.get("precision"), T_train=self.num_timesteps, T_gen=self.num_sampling_steps,
+        )
+
+    def prenet(self, z: torch.Tensor) -> torch.Tensor:
+        """z [B, 1024, Z] -> [B, 16, Z]  (DAL:112-143 == DAL:169-200)."""
+        if self.act_model_type == "conv_fc":
+            B, S, Cz = z.shape
+            s = S // self.n_frames
+            x = z.reshape(B * self.n_frames, s, Cz).reshape(B * self.n_frames, self.w, s // self.w, Cz)
+            x = x.permute(0, 3, 1, 2)  # (b t) c w h
+            x = self.conv(x)
+            x = self.fc(x.reshape(x.shape[0], -1))
+            x = x.reshape(B, self.n_frames, -1).permute(0, 2, 1)
+            x = self.interpolate(x).permute(0, 2, 1)
+            return self.refine(x)
+        if self.act_model_type == "conv_ori":
+            B, S, Cz = z.shape
+            s = S // self.n_frames
+            x = z.reshape(B, self.n_frames, self.w, s // self.w, Cz).permute(0, 4, 1, 2, 3)  # b c t w h
+            x = self.avg_pool(self.conv_transpose3d(x))
+            return x.permute(0, 2, 3, 4, 1).reshape(B, -1, Cz)
+        if self.act_model_type == "conv2":
+            return self.conv(z)
+        if self.act_model_type == "fc2":
+            return self.fc(z.transpose(1, 2)).transpose(1, 2)
+        raise NotImplementedError
+
+    def forward(self, target, z, task_mode=None, text_latents=None):
+        _require_cuda(z, "DiffActLoss.forward")
+        bsz, seq_len, _ = target.shape
+        z = self.prenet(z)
+        target = target.reshape(bsz * seq_len, -1)
+        z = z.reshape(bsz * seq_len, -1)
+        t = torch.randint(0, self.num_timesteps, (target.shape[0],), device=target.device)  # DAL:148-153
+        noise = torch.randn_like(target, dtype=torch.float32)  # GD:761
+        with torch.cuda.device(z.device):
+            # plain mean over rows (DAL:160-164): mask = None
+            return _FusedLoss.apply(self.net, target.float(), z, None, t, noise, *self.net.ordered_params())
+
+    @torch.no_grad()
+    def sample(self, z, temperature=1.0, cfg=1.0, text_latents=None):
+        z = self.prenet(z)
+        bsz, seq_len, _ = z.shape
+        z = z.reshape(bsz * seq_len, -1)
+        out = sample_rows(self.net, z, self.in_channels, self.num_sampling_steps, temperature, cfg, clip_denoised=True)
+        return out.reshape(bsz, seq_len, -1)

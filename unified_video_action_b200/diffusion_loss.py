@@ -1,0 +1,256 @@
+"""Drop-in ``DiffLoss`` backed by libuva_head.so (B200 / sm_100a).
+
+Mirrors the reference ``DiffLoss`` (diffusion_loss.py, "DL"): same constructor arguments
+(DL:11-42), the same ``state_dict`` keys and shapes under ``net.*`` (DL:222-235), the same
+``forward(target, z, mask, ...)`` (DL:44-66) and ``sample(z, temperature, cfg, ...)`` (DL:68-90)
+signatures and the same RNG call order (CPU ``randn`` for the start noise, one CUDA ``randn`` per
+denoise step, ``randint`` then ``randn`` in training).  All arithmetic runs in the CUDA library;
+there is no PyTorch fallback.
+"""
+from __future__ import annotations
+
+import os
+from typing import List, Optional
+
+import torch
+import torch.nn as nn
+
+from . import _lib
+
+
+def _mode_from(precision: Optional[str]) -> int:
+    p = (precision or os.environ.get("UVA_B200_PRECISION", "bf16")).lower()
+    if p in ("bf16", "bfloat16"):
+        return _lib.MODE_BF16
+    if p in ("fp32", "float32"):
+        return _lib.MODE_FP32
+    raise ValueError(f"precision must be 'bf16' or 'fp32', got {precision!r}")
+
+
+def _require_cuda(t: torch.Tensor, what: str) -> None:
+    if t.device.type != "cuda":
+        raise RuntimeError(f"{what}: the B200 diffusion head runs on CUDA (sm_100a) only; there is no CPU fallback")
+
+
+class _TimestepEmbedder(nn.Module):
+    """Parameter holder with the names of the reference TimestepEmbedder (DL:97-139)."""
+
+    def __init__(self, hidden_size: int, frequency_embedding_size: int = 256):
+        super().__init__()
+        self.mlp = nn.Sequential(
+            nn.Linear(frequency_embedding_size, hidden_size, bias=True),
+            nn.SiLU(),
+            nn.Linear(hidden_size, hidden_size, bias=True),
+        )
+        self.frequency_embedding_size = frequency_embedding_size
+
+
+class _ResBlock(nn.Module):
+    """Parameter holder with the names of the reference ResBlock (DL:142-167)."""
+
+    def __init__(self, channels: int):
+        super().__init__()
+        self.channels = channels
+        self.in_ln = nn.LayerNorm(channels, eps=1e-6)
+        self.mlp = nn.Sequential(
+            nn.Linear(channels, channels, bias=True), nn.SiLU(), nn.Linear(channels, channels, bias=True)
+        )
+        self.adaLN_modulation = nn.Sequential(nn.SiLU(), nn.Linear(channels, 3 * channels, bias=True))
+
+
+class _FinalLayer(nn.Module):
+    """Parameter holder with the names of the reference FinalLayer (DL:170-189)."""
+
+    def __init__(self, model_channels: int, out_channels: int):
+        super().__init__()
+        self.norm_final = nn.LayerNorm(model_channels, elementwise_affine=False, eps=1e-6)
+        self.linear = nn.Linear(model_channels, out_channels, bias=True)
+        self.adaLN_modulation = nn.Sequential(nn.SiLU(), nn.Linear(model_channels, 2 * model_channels, bias=True))
+
+
+def param_names(depth: int) -> List[str]:
+    """Parameter names of ``SimpleMLPAdaLN`` in the order the C ABI expects (reference
+    state_dict order, DL:222-235)."""
+    names = [
+        "time_embed.mlp.0.weight", "time_embed.mlp.0.bias", "time_embed.mlp.2.weight", "time_embed.mlp.2.bias",
+        "cond_embed.weight", "cond_embed.bias", "input_proj.weight", "input_proj.bias",
+    ]
+    for i in range(depth):
+        p = f"res_blocks.{i}."
+        names += [p + s for s in (
+            "in_ln.weight", "in_ln.bias", "mlp.0.weight", "mlp.0.bias", "mlp.2.weight", "mlp.2.bias",
+            "adaLN_modulation.1.weight", "adaLN_modulation.1.bias")]
+    names += ["final_layer.linear.weight", "final_layer.linear.bias",
+              "final_layer.adaLN_modulation.1.weight", "final_layer.adaLN_modulation.1.bias"]
+    return names
+
+
+class SimpleMLPAdaLN(nn.Module):
+    """The AdaLN-MLP denoiser (DL:192-293).  Holds the fp32 ``nn.Parameter``s under the reference
+    names (so checkpoints, EMA and optimizers work unchanged) and evaluates through the CUDA head."""
+
+    def __init__(self, in_channels, model_channels, out_channels, z_channels, num_res_blocks,
+                 grad_checkpointing=False, precision: Optional[str] = None, T_train: int = 1000, T_gen: int = 100):
+        super().__init__()
+        if out_channels != 2 * in_channels:
+            raise ValueError("the B200 head implements learn_sigma heads only: out_channels must be 2*in_channels")
+        self.in_channels = in_channels
+        self.model_channels = model_channels
+        self.out_channels = out_channels
+        self.z_channels = z_channels
+        self.num_res_blocks = num_res_blocks
+        self.grad_checkpointing = grad_checkpointing  # accepted; the fused backward keeps what it needs
+        self.time_embed = _TimestepEmbedder(model_channels)
+        self.cond_embed = nn.Linear(z_channels, model_channels)
+        self.input_proj = nn.Linear(in_channels, model_channels)
+        self.res_blocks = nn.ModuleList([_ResBlock(model_channels) for _ in range(num_res_blocks)])
+        self.final_layer = _FinalLayer(model_channels, out_channels)
+        self.initialize_weights()
+        self._mode = _mode_from(precision)
+        self._T = (T_train, T_gen)
+        self._head: Optional[_lib.Head] = None
+        self._packed_key = None
+        self._names = param_names(num_res_blocks)
+
+    def initialize_weights(self):
+        """Same scheme as DL:237-259: Xavier-uniform Linears with zero bias, N(0, 0.02) timestep MLP,
+        zero AdaLN modulation layers and zero output layer."""
+        def _basic_init(m):
+            if isinstance(m, nn.Linear):
+                torch.nn.init.xavier_uniform_(m.weight)
+                if m.bias is not None:
+                    nn.init.constant_(m.bias, 0)
+        self.apply(_basic_init)
+        nn.init.normal_(self.time_embed.mlp[0].weight, std=0.02)
+        nn.init.normal_(self.time_embed.mlp[2].weight, std=0.02)
+        for block in self.res_blocks:
+            nn.init.constant_(block.adaLN_modulation[-1].weight, 0)
+            nn.init.constant_(block.adaLN_modulation[-1].bias, 0)
+        nn.init.constant_(self.final_layer.adaLN_modulation[-1].weight, 0)
+        nn.init.constant_(self.final_layer.adaLN_modulation[-1].bias, 0)
+        nn.init.constant_(self.final_layer.linear.weight, 0)
+        nn.init.constant_(self.final_layer.linear.bias, 0)
+
+    # ---- library plumbing -------------------------------------------------------------------
+    def ordered_params(self) -> List[torch.nn.Parameter]:
+        d = dict(self.named_parameters())
+        return [d[n] for n in self._names]
+
+    def head(self) -> _lib.Head:
+        """The CUDA head with up-to-date packed weights (re-packed when any parameter changed:
+        optimizer step, load_state_dict, .to())."""
+        params = self.ordered_params()
+        dev = params[0].device
+        if dev.type != "cuda":
+            raise RuntimeError("the B200 diffusion head runs on CUDA only; move the module to a cuda device")
+        with torch.cuda.device(dev):
+            if self._head is None or self._head.device != dev:
+                self._head = _lib.Head(self.in_channels, self.z_channels, self.model_channels, self.num_res_blocks,
+                                       self._T[0], self._T[1], self._mode)
+                self._packed_key = None
+            key = tuple((p.data_ptr(), p._version) for p in params)
+            if key != self._packed_key:
+                self._head.load_weights(params)
+                self._packed_key = key
+        return self._head
+
+    def forward(self, x, t, c):
+        """DL:261-283.  Inference-only entry (no autograd graph); training goes through
+        ``DiffLoss.forward`` whose fused loss has its own backward."""
+        _require_cuda(x, "SimpleMLPAdaLN.forward")
+        with torch.cuda.device(x.device):
+            return self.head().net_forward(x, t, c)
+
+    def __deepcopy__(self, memo):
+        # EMA copies (copy.deepcopy) must not share the CUDA handle
+        import copy
+
+        cls = self.__class__
+        new = cls.__new__(cls)
+        memo[id(self)] = new
+        for k, v in self.__dict__.items():
+            if k in ("_head", "_packed_key"):
+                new.__dict__[k] = None
+            else:
+                new.__dict__[k] = copy.deepcopy(v, memo)
+        return new
+
+
+class _FusedLoss(torch.autograd.Function):
+    """training_losses + masked mean as one op with a hand-written backward (GD:746-818, DL:64-66)."""
+
+    @staticmethod
+    def forward(ctx, net: SimpleMLPAdaLN, target, z, mask, t, noise, *params):
+        head = net.head()
+        loss = head.loss_fwd(target, z, mask, t, noise)
+        ctx.net = net
+        ctx.save_for_backward(target, z, mask if mask is not None else torch.empty(0, device=z.device), t, noise)
+        ctx.has_mask = mask is not None
+        ctx.z_dtype = z.dtype
+        return loss.reshape(())
+
+    @staticmethod
+    def backward(ctx, dloss):
+        target, z, mask, t, noise = ctx.saved_tensors
+        net = ctx.net
+        head = net.head()
+        params = net.ordered_params()
+        grads = [torch.zeros_like(p, dtype=torch.float32, memory_format=torch.contiguous_format)
+                 if p.requires_grad else None for p in params]
+        dz = head.loss_bwd(dloss.float(), target, z, mask if ctx.has_mask else None, t, noise, grads)
+        return (None, None, dz.to(ctx.z_dtype) if ctx.needs_input_grad[2] else None, None, None, None, *grads)
+
+
+class DiffLoss(nn.Module):
+    """Diffusion Loss (video-latent head) — drop-in for the reference class (DL:8-90)."""
+
+    def __init__(self, target_channels, z_channels, depth, width, num_sampling_steps,
+                 grad_checkpointing=False, **kwargs):
+        super().__init__()
+        self.n_frames = kwargs["n_frames"]
+        self.language_emb_model = kwargs["language_emb_model"]
+        self.language_emb_model_type = kwargs["language_emb_model_type"]
+        self.in_channels = target_channels
+        self.num_timesteps = 1000  # train_diffusion.num_timesteps (DI:11-20 default diffusion_steps)
+        self.net = SimpleMLPAdaLN(
+            in_channels=target_channels, model_channels=width, out_channels=target_channels * 2,
+            z_channels=z_channels, num_res_blocks=depth, grad_checkpointing=grad_checkpointing,
+            precision=kwargs.get("precision"), T_train=self.num_timesteps, T_gen=int(num_sampling_steps),
+        )
+        self.num_sampling_steps = int(num_sampling_steps)
+
+    def forward(self, target, z, mask=None, conf_score=None, text_latents=None):
+        _require_cuda(z, "DiffLoss.forward")
+        bsz, seq_len, _ = target.shape
+        target = target.reshape(bsz * seq_len, -1)
+        z = z.reshape(bsz * seq_len, -1)
+        mask = mask.reshape(bsz * seq_len)  # like DL:49 a mask is required
+        # same draws, same order as the reference: t (DL:51), then noise = randn_like(x_start) (GD:761)
+        t = torch.randint(0, self.num_timesteps, (target.shape[0],), device=target.device)
+        noise = torch.randn_like(target, dtype=torch.float32)
+        with torch.cuda.device(z.device):
+            return _FusedLoss.apply(self.net, target.float(), z, mask.float(), t, noise, *self.net.ordered_params())
+
+    @torch.no_grad()
+    def sample(self, z, temperature=1.0, cfg=1.0, text_latents=None):
+        return sample_rows(self.net, z, self.in_channels, self.num_sampling_steps, temperature, cfg, clip_denoised=False)
+
+
+@torch.no_grad()
+def sample_rows(net: SimpleMLPAdaLN, z, C: int, steps: int, temperature: float, cfg: float, clip_denoised: bool):
+    """The sampling tail shared by DiffLoss.sample (DL:68-90) and DiffActLoss.sample (DAL:207-227):
+    start noise from the CPU generator moved to the GPU, then the 100-step DDPM loop."""
+    _require_cuda(z, "sample")
+    dev = z.device
+    N = z.shape[0]
+    if not cfg == 1.0:
+        noise = torch.randn(N // 2, C).to(dev)
+        noise = torch.cat([noise, noise], dim=0)
+    else:
+        noise = torch.randn(N, C).to(dev)
+    # one CUDA randn per step, as th.randn_like(x) inside p_sample (GD:431)
+    step_noise = torch.empty(steps, N, C, dtype=torch.float32, device=dev)
+    for k in range(steps):
+        torch.randn(N, C, out=step_noise[k])
+    with torch.cuda.device(dev):
+        return net.head().sample(z, noise, step_noise, temperature=temperature, cfg=cfg, clip_denoised=clip_denoised)
