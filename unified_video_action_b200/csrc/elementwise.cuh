@@ -102,18 +102,28 @@ k_input_proj(const float* __restrict__ x, const float* __restrict__ Wi, const fl
 #pragma unroll
       for (int c = 0; c < 16; ++c) w[q][c] = (c < C) ? Wi[(int64_t)(j0 + q) * C + c] : 0.f;
     }
+#pragma unroll 2
     for (int rr = 0; rr < IP_ROWS; ++rr) {
       const int64_t r = r0 + rr;
       if (r >= rows) break;
-      const int64_t rs = (half > 0) ? (r % half) : r;
+      const int64_t rs = (half > 0 && r >= half) ? (r - half) : r;  // rows < 2 * half
+      float xv[16];
+      if (C == 16) {
+        const float4* xp = reinterpret_cast<const float4*>(x + rs * 16);
+#pragma unroll
+        for (int c4 = 0; c4 < 4; ++c4) {
+          const float4 t = __ldg(xp + c4);
+          xv[4 * c4] = t.x; xv[4 * c4 + 1] = t.y; xv[4 * c4 + 2] = t.z; xv[4 * c4 + 3] = t.w;
+        }
+      } else {
+#pragma unroll
+        for (int c = 0; c < 16; ++c) xv[c] = (c < C) ? __ldg(x + rs * C + c) : 0.f;
+      }
       float acc[4] = {b[0], b[1], b[2], b[3]};
 #pragma unroll
       for (int c = 0; c < 16; ++c) {
-        if (c < C) {
-          const float xv = __ldg(x + rs * C + c);
 #pragma unroll
-          for (int q = 0; q < 4; ++q) acc[q] = fmaf(xv, w[q][c], acc[q]);
-        }
+        for (int q = 0; q < 4; ++q) acc[q] = fmaf(xv[c], w[q][c], acc[q]);
       }
       *reinterpret_cast<float4*>(h + r * W + j0) = make_float4(acc[0], acc[1], acc[2], acc[3]);
     }

@@ -10,8 +10,10 @@
 //                64-wide k-block, tcgen05.commit releases the smem slot / publishes the accumulator;
 //   * warp 2  : TMEM allocator (2 accumulator stages of BN columns: epilogue of tile i overlaps
 //                the MMAs of tile i+1);
-//   * warps 4-7: epilogue — tcgen05.ld (lane = row), transposed through a per-warp padded smem
-//                patch so that global accesses are row-contiguous (coalesced), fused epilogue math.
+//   * warps 4-11: epilogue — 8 warps = 4 TMEM lane quarters x 2 column halves; tcgen05.ld gives
+//                each thread 32 consecutive columns of its own row; the fused epilogue works on that
+//                row segment with 16-byte vector loads/stores (operand loads are issued before the
+//                TMEM load so their latency overlaps it).
 #pragma once
 #include "common.cuh"
 #include "epilogue.cuh"
@@ -20,7 +22,7 @@ namespace uva {
 
 constexpr int UG_BM = 128;
 constexpr int UG_BK = 64;  // 64 bf16 = 128 bytes = one swizzle row
-constexpr int UG_THREADS = 256;
+constexpr int UG_THREADS = 384;
 
 template <int BN>
 struct UmmaCfg {
@@ -28,10 +30,10 @@ struct UmmaCfg {
   static constexpr int kStageBytesB = BN * UG_BK * 2;
   static constexpr int kStageBytes = kStageBytesA + kStageBytesB;
   static constexpr int kStages = (BN >= 256) ? 4 : (BN >= 128 ? 6 : 8);
-  static constexpr int kPatchBytes = 4 * 32 * 33 * 4;  // 4 epilogue warps x [32][33] words
   static constexpr int kBarBytes = 256;
-  static constexpr int kSmemBytes = 1024 /*align slack*/ + kStages * kStageBytes + kPatchBytes + kBarBytes;
+  static constexpr int kSmemBytes = 1024 /*align slack*/ + kStages * kStageBytes + kBarBytes;
   static constexpr uint32_t kTmemCols = (2 * BN <= 32) ? 32 : (2 * BN <= 64) ? 64 : (2 * BN <= 128) ? 128 : (2 * BN <= 256) ? 256 : 512;
+  static constexpr int kColGroups = (BN >= 64) ? 2 : 1;  // epilogue warps per lane quarter
 };
 
 // tile id -> (m_blk, n_blk): groups of `gm` row panels; inside a group the row panel varies
@@ -48,6 +50,110 @@ __device__ __forceinline__ void ug_tile_coords(int64_t tile, int64_t m_tiles, in
   m_blk = m_first + (rem - (int64_t)n_blk * rows_in_group);
 }
 
+// ------------------------------------------------------------------------------------------
+// Row-segment epilogue: thread owns acc[0..31] = D[row, col0 .. col0+31].
+// ------------------------------------------------------------------------------------------
+template <int KIND, typename TA>
+struct RowEpi {
+  static constexpr bool kNeedsPrefetch = (KIND == EPI_GATED_RES);
+  struct Pre {
+    float4 h[8];
+    uint4 g[4];
+  };
+
+  __device__ static __forceinline__ void prefetch(const EpiArgs& e, int64_t row, int col0, Pre& p) {
+    if constexpr (KIND == EPI_GATED_RES) {
+      const float4* hp = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(e.out) + row * e.ldo + col0);
+      const uint4* gp = reinterpret_cast<const uint4*>(reinterpret_cast<const bf16*>(e.aux) + row * e.ldaux + col0);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) p.h[i] = hp[i];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) p.g[i] = gp[i];
+    }
+  }
+
+  __device__ static __forceinline__ void bias32(const EpiArgs& e, int col0, float (&b)[32]) {
+    if (e.bias != nullptr) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const float4 t = __ldg(reinterpret_cast<const float4*>(e.bias + col0) + i);
+        b[4 * i] = t.x; b[4 * i + 1] = t.y; b[4 * i + 2] = t.z; b[4 * i + 3] = t.w;
+      }
+    } else {
+#pragma unroll
+      for (int i = 0; i < 32; ++i) b[i] = 0.f;
+    }
+  }
+
+  __device__ static __forceinline__ void store(const EpiArgs& e, int64_t row, int col0, const uint32_t (&v)[32], const Pre& p) {
+    constexpr bool kVec = (sizeof(TA) == 2) || KIND == EPI_STORE_F32;
+    if (!kVec || col0 + 32 > e.n_valid || KIND == EPI_ACCUM_F32 || KIND == EPI_ATOMIC_F32) {
+      // generic tail / rarely used kinds: scalar per-element epilogue
+#pragma unroll
+      for (int j = 0; j < 32; ++j) Epi<KIND, TA>::apply(e, row, col0 + j, __uint_as_float(v[j]));
+      return;
+    }
+    float b[32];
+    bias32(e, col0, b);
+    if constexpr (KIND == EPI_STORE_F32) {
+      float4* o = reinterpret_cast<float4*>(reinterpret_cast<float*>(e.out) + row * e.ldo + col0);
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+        o[i] = make_float4(__uint_as_float(v[4 * i]) + b[4 * i], __uint_as_float(v[4 * i + 1]) + b[4 * i + 1],
+                           __uint_as_float(v[4 * i + 2]) + b[4 * i + 2], __uint_as_float(v[4 * i + 3]) + b[4 * i + 3]);
+    } else if constexpr (KIND == EPI_GATED_RES) {
+      float4* o = reinterpret_cast<float4*>(reinterpret_cast<float*>(e.out) + row * e.ldo + col0);
+      const __nv_bfloat162* g2 = reinterpret_cast<const __nv_bfloat162*>(p.g);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const float2 ga = __bfloat1622float2(g2[2 * i]);
+        const float2 gb = __bfloat1622float2(g2[2 * i + 1]);
+        float4 r = p.h[i];
+        r.x = fmaf(ga.x, __uint_as_float(v[4 * i]) + b[4 * i], r.x);
+        r.y = fmaf(ga.y, __uint_as_float(v[4 * i + 1]) + b[4 * i + 1], r.y);
+        r.z = fmaf(gb.x, __uint_as_float(v[4 * i + 2]) + b[4 * i + 2], r.z);
+        r.w = fmaf(gb.y, __uint_as_float(v[4 * i + 3]) + b[4 * i + 3], r.w);
+        o[i] = r;
+      }
+    } else {
+      // 16-bit outputs: out = f(acc + bias) packed to bf16, 4 x 16-byte stores
+      float x[32];
+#pragma unroll
+      for (int j = 0; j < 32; ++j) x[j] = __uint_as_float(v[j]) + b[j];
+      if constexpr (KIND == EPI_SILU_SAVE) {
+        uint4* o2 = reinterpret_cast<uint4*>(reinterpret_cast<bf16*>(e.out2) + row * e.ldo2 + col0);
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+          o2[i] = make_uint4(pack_bf16x2(x[8 * i], x[8 * i + 1]), pack_bf16x2(x[8 * i + 2], x[8 * i + 3]),
+                             pack_bf16x2(x[8 * i + 4], x[8 * i + 5]), pack_bf16x2(x[8 * i + 6], x[8 * i + 7]));
+      }
+      if constexpr (KIND == EPI_SILU_ACT || KIND == EPI_SILU_SAVE) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) x[j] = __fdividef(x[j], 1.0f + __expf(-x[j]));
+      }
+      if constexpr (KIND == EPI_DSILU_ACT) {
+        const uint4* ap = reinterpret_cast<const uint4*>(reinterpret_cast<const bf16*>(e.aux) + row * e.ldaux + col0);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const uint4 t = ap[i];
+          const __nv_bfloat162* t2 = reinterpret_cast<const __nv_bfloat162*>(&t);
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const float2 pq = __bfloat1622float2(t2[q]);
+            x[8 * i + 2 * q] = __uint_as_float(v[8 * i + 2 * q]) * dsilu_f(pq.x);
+            x[8 * i + 2 * q + 1] = __uint_as_float(v[8 * i + 2 * q + 1]) * dsilu_f(pq.y);
+          }
+        }
+      }
+      uint4* o = reinterpret_cast<uint4*>(reinterpret_cast<bf16*>(e.out) + row * e.ldo + col0);
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+        o[i] = make_uint4(pack_bf16x2(x[8 * i], x[8 * i + 1]), pack_bf16x2(x[8 * i + 2], x[8 * i + 3]),
+                          pack_bf16x2(x[8 * i + 4], x[8 * i + 5]), pack_bf16x2(x[8 * i + 6], x[8 * i + 7]));
+    }
+  }
+};
+
 template <int BN, int KIND, typename TA>
 __global__ void __launch_bounds__(UG_THREADS, 1)
 umma_gemm_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
@@ -57,8 +163,7 @@ umma_gemm_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* stage_base = smem;
-  uint32_t* patch = reinterpret_cast<uint32_t*>(smem + kStages * Cfg::kStageBytes);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kStages * Cfg::kStageBytes + Cfg::kPatchBytes);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kStages * Cfg::kStageBytes);
   uint64_t* full_bar = bars;                  // [kStages]
   uint64_t* empty_bar = bars + kStages;       // [kStages]
   uint64_t* tfull_bar = bars + 2 * kStages;   // [2]
@@ -83,7 +188,7 @@ umma_gemm_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&tfull_bar[s], 1);
-      mbar_init(&tempty_bar[s], 4);
+      mbar_init(&tempty_bar[s], 4 * Cfg::kColGroups);
     }
     fence_mbar_init();
   }
@@ -147,51 +252,32 @@ umma_gemm_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       }
       if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
     }
-  } else if (warp >= 4) {
+  } else if (warp >= 4 && ((warp - 4) >> 2) < Cfg::kColGroups) {
     // ===================== epilogue =====================
-    const int q = warp & 3;  // TMEM lane quarter this warp may access
-    uint32_t* my_patch = patch + q * (32 * 33);
+    const int q = warp & 3;          // TMEM lane quarter this warp may access
+    const int cg = (warp - 4) >> 2;  // column group
+    constexpr int kColsPerGroup = BN / Cfg::kColGroups;
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int64_t tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       int64_t m_blk; int n_blk;
       ug_tile_coords(tile, m_tiles, n_tiles, gm, m_blk, n_blk);
-      const int64_t row0 = m_blk * UG_BM + q * 32;
-      const int n0 = n_blk * BN;
+      const int64_t row = m_blk * UG_BM + q * 32 + lane;
+      const bool row_ok = row < M;
+      const int n0 = n_blk * BN + cg * kColsPerGroup;
+      typename RowEpi<KIND, TA>::Pre pre;
+      if (RowEpi<KIND, TA>::kNeedsPrefetch && row_ok) RowEpi<KIND, TA>::prefetch(ep, row, n0, pre);
       mbar_wait(&tfull_bar[acc], acc_phase);
       tc_fence_after();
-      const uint32_t t_addr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN);
-      constexpr bool kPairs = (sizeof(TA) == 2) && (KIND == EPI_STORE_ACT || KIND == EPI_SILU_ACT ||
-                                                    KIND == EPI_SILU_SAVE || KIND == EPI_DSILU_ACT);
+      const uint32_t t_addr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN + cg * kColsPerGroup);
 #pragma unroll 1
-      for (int c0 = 0; c0 < BN; c0 += 32) {
+      for (int c0 = 0; c0 < kColsPerGroup; c0 += 32) {
         uint32_t v[32];
         tmem_ld_32x32(t_addr + (uint32_t)c0, v);
         tmem_ld_wait();
-        // thread = row `lane`; write my 32 columns into patch[lane][0..31] (row stride 33 words)
-#pragma unroll
-        for (int j = 0; j < 32; ++j) my_patch[lane * 33 + j] = v[j];
-        __syncwarp();
-        if constexpr (kPairs) {
-          // lane handles columns (2*(lane&15), +1) of rows rr + (lane>>4): 2 rows per pass
-#pragma unroll 4
-          for (int rr = 0; rr < 32; rr += 2) {
-            const int r = rr + (lane >> 4);
-            const int cc = 2 * (lane & 15);
-            const float a0 = __uint_as_float(my_patch[r * 33 + cc]);
-            const float a1 = __uint_as_float(my_patch[r * 33 + cc + 1]);
-            const int64_t grow = row0 + r;
-            if (grow < M) Epi<KIND, TA>::apply2(ep, grow, n0 + c0 + cc, a0, a1);
-          }
-        } else {
-#pragma unroll 4
-          for (int r = 0; r < 32; ++r) {
-            const float a0 = __uint_as_float(my_patch[r * 33 + lane]);
-            const int64_t grow = row0 + r;
-            if (grow < M) Epi<KIND, TA>::apply(ep, grow, n0 + c0 + lane, a0);
-          }
-        }
-        __syncwarp();
+        if (row_ok) RowEpi<KIND, TA>::store(ep, row, n0 + c0, v, pre);
+        if (RowEpi<KIND, TA>::kNeedsPrefetch && row_ok && c0 + 32 < kColsPerGroup)
+          RowEpi<KIND, TA>::prefetch(ep, row, n0 + c0 + 32, pre);
       }
       tc_fence_before();
       __syncwarp();

@@ -159,6 +159,11 @@ struct UvaHead {
   int64_t launches = 0;
   PFN_encodeTiled encode = nullptr;
   // optional per-category GEMM timing (bench.py roofline): CUDA event pairs on the launch stream
+  // second stream: two row chunks are processed concurrently so that the HBM-bound row kernels
+  // of one chunk overlap the tensor-bound GEMMs of the other
+  cudaStream_t side = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+  bool overlap = true;
   bool timing = false;
   int cur_cat = 0;
   struct TimedLaunch { int cat; cudaEvent_t a, b; };
@@ -256,6 +261,10 @@ extern "C" int uva_head_create(const UvaHeadDesc* desc, UvaHead** out) {
     long v = atol(e);
     if (v >= 256) h->chunk_rows = (v / 256) * 256;
   }
+  if (const char* e = getenv("UVA_OVERLAP")) h->overlap = atoi(e) != 0;
+  CUDA_TRY(cudaStreamCreateWithFlags(&h->side, cudaStreamNonBlocking));
+  CUDA_TRY(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
+  CUDA_TRY(cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming));
   h->gen = create_schedule(d.T_train, d.T_gen);
   h->train = create_schedule(d.T_train, d.T_train);
   int rc = upload_tables(h->train, h->dtrain, &h->d_tables);
@@ -324,8 +333,12 @@ extern "C" void uva_head_destroy(UvaHead* h) {
   if (!h) return;
   cudaFree(h->d_tables); cudaFree(h->feat); cudaFree(h->temb); cudaFree(h->temb_hidden);
   cudaFree(h->wf); cudaFree(h->wb);
+  if (h->side) cudaStreamDestroy(h->side);
+  if (h->ev_fork) cudaEventDestroy(h->ev_fork);
+  if (h->ev_join) cudaEventDestroy(h->ev_join);
   delete h;
 }
 
 #include "head_infer.inc"
+#include "head_sample.inc"
 #include "head_train.inc"
