@@ -141,10 +141,14 @@ int64_t uva_head_launch_count(const UvaHead* h);
 int uva_head_timing_enable(UvaHead* h, int32_t enable);
 int uva_head_timing_read(UvaHead* h, int32_t category, double* total_ms, int64_t* count);
 
-/* Unit check of the tcgen05 GEMM core: D[M,N] (fp32) = A[M,K] (bf16) . B[N,K]^T (bf16) + bias.
- * N multiple of 32, K multiple of 64. */
+/* Unit check of the tcgen05 GEMM core (bf16 operands, fp32 result), D[M,N]:
+ *   layout 0: A[M,K], B[N,K] (forward form, D = A.B^T + bias; block_n 32 or 256, K multiple of 8);
+ *   layout 1: A[M,K], B[K,N] (data-gradient form, B MN-major; block_n 256);
+ *   layout 2: A[K,M], B[K,N] (weight-gradient form, both MN-major, split-K with vector reductions
+ *             ADDED into D, which the caller zero-fills; block_n 256, bias ignored).
+ * N multiple of block_n. */
 int uva_gemm_bf16_selftest(const void* A, const void* B, const float* bias, float* D, int64_t M,
-                           int32_t N, int32_t K, int32_t block_n, void* stream);
+                           int32_t N, int32_t K, int32_t block_n, int32_t layout, void* stream);
 
 const char* uva_last_error(void);
 const char* uva_build_info(void);

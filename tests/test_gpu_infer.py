@@ -103,6 +103,41 @@ def test_umma_gemm_matches_fp32_matmul(M, N, K, BN):
     assert err <= 2e-4 * float(ref.abs().max()), err
 
 
+@pytest.mark.parametrize("M,N,K", [(128, 256, 64), (300, 768, 1024), (4101, 1024, 3072), (77, 256, 200)])
+def test_umma_gemm_dgrad_layout(M, N, K):
+    """Data-gradient form: A [M,K] K-major, B [K,N] MN-major (the untransposed weight); K tails are
+    zero-filled by TMA."""
+    dev = _cuda()
+    from unified_video_action_b200 import _lib
+
+    g = torch.Generator(device="cpu").manual_seed(7 * M + N + K)
+    A = torch.randn(M, K, generator=g).to(dev).bfloat16()
+    B = (torch.randn(K, N, generator=g) / K ** 0.5).to(dev).bfloat16()
+    bias = torch.randn(N, generator=g).to(dev)
+    D = _lib.gemm_bf16_selftest(A, B, bias, 256, layout=1)
+    ref = A.float() @ B.float() + bias
+    torch.cuda.synchronize()
+    err = float((D - ref).abs().max())
+    assert err <= 2e-4 * float(ref.abs().max()), err
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 256, 64), (1024, 1024, 16384), (3072, 768, 5000), (200, 256, 130)])
+def test_umma_gemm_wgrad_layout(M, N, K):
+    """Weight-gradient form: A [K,M], B [K,N] both MN-major, K = rows (any count), split-K partial
+    sums reduced into D with vector atomics."""
+    dev = _cuda()
+    from unified_video_action_b200 import _lib
+
+    g = torch.Generator(device="cpu").manual_seed(3 * M + N + K)
+    A = torch.randn(K, M, generator=g).to(dev).bfloat16()
+    B = (torch.randn(K, N, generator=g) / K ** 0.5).to(dev).bfloat16()
+    D = _lib.gemm_bf16_selftest(A, B, None, 256, layout=2)
+    ref = A.float().t() @ B.float()
+    torch.cuda.synchronize()
+    err = float((D - ref).abs().max())
+    assert err <= 3e-4 * float(ref.abs().max()), err
+
+
 # ------------------------------------------------------------------------------------------
 # SimpleMLPAdaLN.forward (DL:261-283)
 # ------------------------------------------------------------------------------------------

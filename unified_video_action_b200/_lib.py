@@ -110,7 +110,7 @@ def lib() -> ctypes.CDLL:
         L.uva_head_launch_count.restype = i64
         L.uva_head_launch_count.argtypes = [vp]
         L.uva_gemm_bf16_selftest.restype = ctypes.c_int
-        L.uva_gemm_bf16_selftest.argtypes = [vp, vp, vp, vp, i64, i32, i32, i32, vp]
+        L.uva_gemm_bf16_selftest.argtypes = [vp, vp, vp, vp, i64, i32, i32, i32, i32, vp]
         L.uva_head_timing_enable.restype = ctypes.c_int
         L.uva_head_timing_enable.argtypes = [vp, i32]
         L.uva_head_timing_read.restype = ctypes.c_int
@@ -271,13 +271,17 @@ class Head:
         return dz
 
 
-def gemm_bf16_selftest(A: torch.Tensor, B: torch.Tensor, bias: Optional[torch.Tensor], block_n: int) -> torch.Tensor:
-    """D = A . B^T (+ bias) through the tcgen05 GEMM core; A [M,K] bf16, B [N,K] bf16."""
+def gemm_bf16_selftest(A: torch.Tensor, B: torch.Tensor, bias: Optional[torch.Tensor], block_n: int, layout: int = 0) -> torch.Tensor:
+    """tcgen05 GEMM core unit check.  layout 0: A [M,K], B [N,K] -> A.B^T (+bias); 1: A [M,K], B [K,N] ->
+    A.B; 2: A [K,M], B [K,N] -> A^T.B (split-K, reduced into a zero-filled D)."""
     assert A.dtype == torch.bfloat16 and B.dtype == torch.bfloat16 and A.is_cuda and B.is_cuda
     A, B = A.contiguous(), B.contiguous()
-    M, K = A.shape
-    N = B.shape[0]
-    D = torch.empty(M, N, dtype=torch.float32, device=A.device)
-    _check(lib().uva_gemm_bf16_selftest(A.data_ptr(), B.data_ptr(), _ptr(bias), D.data_ptr(), M, N, K, block_n, _stream()),
+    if layout == 2:
+        K, M = A.shape
+    else:
+        M, K = A.shape
+    N = B.shape[0] if layout == 0 else B.shape[1]
+    D = torch.zeros(M, N, dtype=torch.float32, device=A.device)
+    _check(lib().uva_gemm_bf16_selftest(A.data_ptr(), B.data_ptr(), _ptr(bias), D.data_ptr(), M, N, K, block_n, layout, _stream()),
            "uva_gemm_bf16_selftest")
     return D

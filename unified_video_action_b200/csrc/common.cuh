@@ -37,6 +37,11 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   return *reinterpret_cast<uint32_t*>(&p);
 }
 
+// 16-byte vector reduction to global memory (split-K / accumulate-into-gradient epilogues)
+__device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
 // ----------------------------------------------------------------------------------------------
 // shared-memory address, election
 // ----------------------------------------------------------------------------------------------
@@ -188,10 +193,20 @@ __device__ __forceinline__ uint64_t umma_desc_k_sw128(uint32_t smem_addr) {
   return (uint64_t)((smem_addr >> 4) & 0x3FFFu) | (1ull << 16) | (64ull << 32) | (1ull << 46) |
          (2ull << 61);
 }
+// MN-major, 128-byte-swizzled operand: the tile is stored as atoms of [64 k-rows][64 mn elements =
+// 128 B] (what a 64x64 TMA box of a row-major [K, MN] matrix gives); groups of 8 k-rows = 1024 B
+// (SBO), the next 64-element MN atom starts `atom_bytes` later (LBO).  Canonical form
+// ((8,n),(8,k)):((1,LBO),(8,SBO)) in 16-byte units (CUTLASS mma_traits_sm100.hpp, Major-MN B128).
+__device__ __forceinline__ uint64_t umma_desc_mn_sw128(uint32_t smem_addr, uint32_t atom_bytes) {
+  return (uint64_t)((smem_addr >> 4) & 0x3FFFu) | ((uint64_t)((atom_bytes >> 4) & 0x3FFFu) << 16) |
+         (64ull << 32) | (1ull << 46) | (2ull << 61);
+}
 // Instruction descriptor, kind::f16: D fp32 (bit 4), A bf16 (bit 7), B bf16 (bit 10), both
 // K-major, N >> 3 at bit 17, M >> 4 at bit 24.
-__host__ __device__ constexpr uint32_t umma_idesc_bf16(int M, int N) {
-  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+// a_mn / b_mn: operand is MN-major (bits 15 / 16).
+__host__ __device__ constexpr uint32_t umma_idesc_bf16(int M, int N, bool a_mn = false, bool b_mn = false) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((a_mn ? 1u : 0u) << 15) | ((b_mn ? 1u : 0u) << 16) |
+         ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
 
 }  // namespace uva

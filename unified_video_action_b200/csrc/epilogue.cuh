@@ -13,8 +13,9 @@ struct EpiArgs {
   int64_t ldo = 0;              // row stride of out (elements)
   const void* aux = nullptr;    // second input (gate / saved activation), element type = TA
   int64_t ldaux = 0;
-  void* out2 = nullptr;         // optional second output (pre-activation / transposed copy)
+  void* out2 = nullptr;         // optional second output (pre-activation / un-gated MLP output)
   int64_t ldo2 = 0;
+  const float* res = nullptr;   // residual input of the gated-residual kinds (row stride ldo); null = out
   int32_t n_valid = 0;          // valid output columns (columns >= n_valid are padding)
   float alpha = 1.0f;
 };
@@ -28,6 +29,7 @@ enum EpiKind {
   EPI_ACCUM_F32 = 5,  // out(f32)[r,c] += alpha * acc                            (wgrad accumulate)
   EPI_DSILU_ACT = 6,  // out(TA)[r,c]   = (acc) * SiLU'(aux(TA)[r,c])            (dgrad through SiLU)
   EPI_ATOMIC_F32 = 7, // atomicAdd(out(f32)[r,c], alpha * acc)                   (split-K wgrad)
+  EPI_GATED_SAVE = 8, // q = acc + bias; out2(TA) = q; out(f32) = res + aux * q  (training fwd, DL:167)
 };
 
 template <int KIND, typename TA>
@@ -41,10 +43,12 @@ struct Epi {
       reinterpret_cast<TA*>(e.out)[r * e.ldo + c] = from_f32<TA>(acc + b);
     } else if constexpr (KIND == EPI_SILU_ACT) {
       reinterpret_cast<TA*>(e.out)[r * e.ldo + c] = from_f32<TA>(silu_f(acc + b));
-    } else if constexpr (KIND == EPI_GATED_RES) {
+    } else if constexpr (KIND == EPI_GATED_RES || KIND == EPI_GATED_SAVE) {
       const float g = to_f32(reinterpret_cast<const TA*>(e.aux)[r * e.ldaux + c]);
       float* o = reinterpret_cast<float*>(e.out) + r * e.ldo + c;
-      *o = *o + g * (acc + b);
+      const float* rp = (e.res != nullptr ? e.res : reinterpret_cast<const float*>(e.out)) + r * e.ldo + c;
+      if constexpr (KIND == EPI_GATED_SAVE) reinterpret_cast<TA*>(e.out2)[r * e.ldo2 + c] = from_f32<TA>(acc + b);
+      *o = *rp + g * (acc + b);
     } else if constexpr (KIND == EPI_SILU_SAVE) {
       const float p = acc + b;
       reinterpret_cast<TA*>(e.out2)[r * e.ldo2 + c] = from_f32<TA>(p);

@@ -26,10 +26,12 @@ __device__ __forceinline__ void sg_load4<bf16>(const bf16* p, float (&v)[4]) {
 }
 
 // K must be a multiple of 4 (tails in K are zero-filled per 4-element group); lda/ldb multiples of 4.
-template <int KIND, typename TA, typename TIn>
+// A_MN / B_MN: the operand is stored [K, MN] row-major (element (m,k) at A[k*lda + m]); then M (N)
+// must be a multiple of 4 and K is free.
+template <int KIND, typename TA, typename TIn, bool A_MN = false, bool B_MN = false>
 __global__ void __launch_bounds__(SG_THREADS)
 sgemm_tn_kernel(const TIn* __restrict__ A, int64_t lda, const TIn* __restrict__ B, int64_t ldb,
-                int64_t M, int N, int K, EpiArgs ep) {
+                int64_t M, int N, int K, int kper, EpiArgs ep) {
   __shared__ float As[SG_BK][SG_BM + 4];
   __shared__ float Bs[SG_BK][SG_BN + 4];
   const int tid = threadIdx.x;
@@ -45,17 +47,32 @@ sgemm_tn_kernel(const TIn* __restrict__ A, int64_t lda, const TIn* __restrict__ 
 #pragma unroll
     for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
 
-  for (int k0 = 0; k0 < K; k0 += SG_BK) {
+  const int kbeg = blockIdx.z * kper;
+  if (kbeg < K && kbeg + kper < K) K = kbeg + kper;  // this split's k range is [kbeg, K)
+  for (int k0 = kbeg; k0 < K; k0 += SG_BK) {
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
       const int r = lrow + 64 * h;
+      const int idx = tid + SG_THREADS * h;  // MN-major: 16 k x 32 float4 along mn
+      const int tk = idx / 32, tm = (idx % 32) * 4;
       float va[4] = {0.f, 0.f, 0.f, 0.f}, vb[4] = {0.f, 0.f, 0.f, 0.f};
-      if (m0 + r < M && k0 + lk < K) sg_load4<TIn>(A + (m0 + r) * lda + k0 + lk, va);
-      if (n0 + r < N && k0 + lk < K) sg_load4<TIn>(B + (int64_t)(n0 + r) * ldb + k0 + lk, vb);
+      if constexpr (A_MN) {
+        if (m0 + tm < M && k0 + tk < K) sg_load4<TIn>(A + (int64_t)(k0 + tk) * lda + m0 + tm, va);
 #pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        As[lk + q][r] = va[q];
-        Bs[lk + q][r] = vb[q];
+        for (int q = 0; q < 4; ++q) As[tk][tm + q] = va[q];
+      } else {
+        if (m0 + r < M && k0 + lk < K) sg_load4<TIn>(A + (m0 + r) * lda + k0 + lk, va);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) As[lk + q][r] = va[q];
+      }
+      if constexpr (B_MN) {
+        if (n0 + tm < N && k0 + tk < K) sg_load4<TIn>(B + (int64_t)(k0 + tk) * ldb + n0 + tm, vb);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) Bs[tk][tm + q] = vb[q];
+      } else {
+        if (n0 + r < N && k0 + lk < K) sg_load4<TIn>(B + (int64_t)(n0 + r) * ldb + k0 + lk, vb);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) Bs[lk + q][r] = vb[q];
       }
     }
     __syncthreads();
@@ -88,12 +105,19 @@ sgemm_tn_kernel(const TIn* __restrict__ A, int64_t lda, const TIn* __restrict__ 
   }
 }
 
-template <int KIND, typename TA, typename TIn>
+template <int KIND, typename TA, typename TIn, bool A_MN = false, bool B_MN = false>
 inline cudaError_t sgemm_tn(const TIn* A, int64_t lda, const TIn* B, int64_t ldb, int64_t M, int N,
-                            int K, const EpiArgs& ep, cudaStream_t st) {
+                            int64_t K, const EpiArgs& ep, cudaStream_t st) {
   if (M <= 0 || N <= 0) return cudaSuccess;
-  dim3 grid((N + SG_BN - 1) / SG_BN, (unsigned)((M + SG_BM - 1) / SG_BM));
-  sgemm_tn_kernel<KIND, TA, TIn><<<grid, SG_THREADS, 0, st>>>(A, lda, B, ldb, M, N, K, ep);
+  // split-K for the reducing epilogue (weight gradients: M x N small, K = rows long)
+  int splits = 1;
+  if (KIND == EPI_ATOMIC_F32) {
+    const int64_t tiles = ((N + SG_BN - 1) / SG_BN) * ((M + SG_BM - 1) / SG_BM);
+    while (splits < 64 && tiles * splits < 296 && K / (splits * 2) >= 256) splits *= 2;
+  }
+  const int64_t kper = ((K + splits - 1) / splits + SG_BK - 1) / SG_BK * SG_BK;
+  dim3 grid((N + SG_BN - 1) / SG_BN, (unsigned)((M + SG_BM - 1) / SG_BM), splits);
+  sgemm_tn_kernel<KIND, TA, TIn, A_MN, B_MN><<<grid, SG_THREADS, 0, st>>>(A, lda, B, ldb, M, N, (int)K, (int)kper, ep);
   return cudaGetLastError();
 }
 

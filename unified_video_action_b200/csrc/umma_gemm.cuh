@@ -55,15 +55,15 @@ __device__ __forceinline__ void ug_tile_coords(int64_t tile, int64_t m_tiles, in
 // ------------------------------------------------------------------------------------------
 template <int KIND, typename TA>
 struct RowEpi {
-  static constexpr bool kNeedsPrefetch = (KIND == EPI_GATED_RES);
+  static constexpr bool kNeedsPrefetch = (KIND == EPI_GATED_RES || KIND == EPI_GATED_SAVE);
   struct Pre {
     float4 h[8];
     uint4 g[4];
   };
 
   __device__ static __forceinline__ void prefetch(const EpiArgs& e, int64_t row, int col0, Pre& p) {
-    if constexpr (KIND == EPI_GATED_RES) {
-      const float4* hp = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(e.out) + row * e.ldo + col0);
+    if constexpr (KIND == EPI_GATED_RES || KIND == EPI_GATED_SAVE) {
+      const float4* hp = reinterpret_cast<const float4*>((e.res != nullptr ? e.res : reinterpret_cast<const float*>(e.out)) + row * e.ldo + col0);
       const uint4* gp = reinterpret_cast<const uint4*>(reinterpret_cast<const bf16*>(e.aux) + row * e.ldaux + col0);
 #pragma unroll
       for (int i = 0; i < 8; ++i) p.h[i] = hp[i];
@@ -86,7 +86,17 @@ struct RowEpi {
   }
 
   __device__ static __forceinline__ void store(const EpiArgs& e, int64_t row, int col0, const uint32_t (&v)[32], const Pre& p) {
-    constexpr bool kVec = (sizeof(TA) == 2) || KIND == EPI_STORE_F32;
+    constexpr bool kVec = (sizeof(TA) == 2) || KIND == EPI_STORE_F32;  // (gated kinds: TA is bf16 here)
+    if constexpr (KIND == EPI_ATOMIC_F32) {
+      if (col0 + 32 <= e.n_valid) {
+        float* o = reinterpret_cast<float*>(e.out) + row * e.ldo + col0;
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+          red_add_v4(o + 4 * i, e.alpha * __uint_as_float(v[4 * i]), e.alpha * __uint_as_float(v[4 * i + 1]),
+                     e.alpha * __uint_as_float(v[4 * i + 2]), e.alpha * __uint_as_float(v[4 * i + 3]));
+        return;
+      }
+    }
     if (!kVec || col0 + 32 > e.n_valid || KIND == EPI_ACCUM_F32 || KIND == EPI_ATOMIC_F32) {
       // generic tail / rarely used kinds: scalar per-element epilogue
 #pragma unroll
@@ -101,9 +111,18 @@ struct RowEpi {
       for (int i = 0; i < 8; ++i)
         o[i] = make_float4(__uint_as_float(v[4 * i]) + b[4 * i], __uint_as_float(v[4 * i + 1]) + b[4 * i + 1],
                            __uint_as_float(v[4 * i + 2]) + b[4 * i + 2], __uint_as_float(v[4 * i + 3]) + b[4 * i + 3]);
-    } else if constexpr (KIND == EPI_GATED_RES) {
+    } else if constexpr (KIND == EPI_GATED_RES || KIND == EPI_GATED_SAVE) {
       float4* o = reinterpret_cast<float4*>(reinterpret_cast<float*>(e.out) + row * e.ldo + col0);
       const __nv_bfloat162* g2 = reinterpret_cast<const __nv_bfloat162*>(p.g);
+      if constexpr (KIND == EPI_GATED_SAVE) {
+        uint4* o2 = reinterpret_cast<uint4*>(reinterpret_cast<bf16*>(e.out2) + row * e.ldo2 + col0);
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+          o2[i] = make_uint4(pack_bf16x2(__uint_as_float(v[8 * i]) + b[8 * i], __uint_as_float(v[8 * i + 1]) + b[8 * i + 1]),
+                             pack_bf16x2(__uint_as_float(v[8 * i + 2]) + b[8 * i + 2], __uint_as_float(v[8 * i + 3]) + b[8 * i + 3]),
+                             pack_bf16x2(__uint_as_float(v[8 * i + 4]) + b[8 * i + 4], __uint_as_float(v[8 * i + 5]) + b[8 * i + 5]),
+                             pack_bf16x2(__uint_as_float(v[8 * i + 6]) + b[8 * i + 6], __uint_as_float(v[8 * i + 7]) + b[8 * i + 7]));
+      }
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
         const float2 ga = __bfloat1622float2(g2[2 * i]);
@@ -154,12 +173,17 @@ struct RowEpi {
   }
 };
 
-template <int BN, int KIND, typename TA>
+// A_MN / B_MN: the operand is stored [K, MN] row-major ("MN-major": activations / output gradients
+// in the weight-gradient GEMM, the untransposed weight in the data-gradient GEMM); its tensor map
+// has 64x64 boxes and one k-block is loaded as BM/64 (BN/64) atoms.  `splits` > 1: split-K, work
+// item = (tile, split); only the reducing epilogue kinds may be used with it.
+template <int BN, int KIND, typename TA, bool A_MN = false, bool B_MN = false>
 __global__ void __launch_bounds__(UG_THREADS, 1)
 umma_gemm_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                    int64_t M, int N, int K, int gm, EpiArgs ep) {
+                    int64_t M, int N, int K, int gm, int splits, EpiArgs ep) {
   using Cfg = UmmaCfg<BN>;
   constexpr int kStages = Cfg::kStages;
+  constexpr uint32_t kAtomBytes = 64 * UG_BK * 2;  // one [64 k][64 mn] atom of an MN-major operand
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* stage_base = smem;
@@ -174,8 +198,9 @@ umma_gemm_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   const int lane = threadIdx.x & 31;
   const int64_t m_tiles = (M + UG_BM - 1) / UG_BM;
   const int n_tiles = N / BN;
-  const int64_t num_tiles = m_tiles * n_tiles;
-  const int num_kb = K / UG_BK;
+  const int64_t num_tiles = m_tiles * n_tiles * splits;  // work items
+  const int num_kb_total = (K + UG_BK - 1) / UG_BK;       // K tail: TMA zero-fills out of bounds
+  const int kb_per = (num_kb_total + splits - 1) / splits;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
@@ -203,49 +228,69 @@ umma_gemm_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int64_t tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      for (int64_t item = blockIdx.x; item < num_tiles; item += gridDim.x) {
         int64_t m_blk; int n_blk;
+        const int64_t tile = item / splits;
+        const int split = (int)(item - tile * splits);
         ug_tile_coords(tile, m_tiles, n_tiles, gm, m_blk, n_blk);
         const int32_t m0 = (int32_t)(m_blk * UG_BM);
         const int32_t n0 = n_blk * BN;
-        for (int kb = 0; kb < num_kb; ++kb) {
+        const int kb0 = split * kb_per;
+        const int kb1 = (kb0 + kb_per < num_kb_total) ? kb0 + kb_per : num_kb_total;
+        for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1u);
           uint8_t* sa = stage_base + stage * Cfg::kStageBytes;
           uint8_t* sb = sa + Cfg::kStageBytesA;
           mbar_arrive_expect_tx(&full_bar[stage], (uint32_t)Cfg::kStageBytes);
-          tma_load_2d(sa, &tmA, &full_bar[stage], kb * UG_BK, m0);
-          tma_load_2d(sb, &tmB, &full_bar[stage], kb * UG_BK, n0);
+          if constexpr (A_MN) {
+#pragma unroll
+            for (int a = 0; a < UG_BM / 64; ++a) tma_load_2d(sa + a * kAtomBytes, &tmA, &full_bar[stage], m0 + 64 * a, kb * UG_BK);
+          } else {
+            tma_load_2d(sa, &tmA, &full_bar[stage], kb * UG_BK, m0);
+          }
+          if constexpr (B_MN) {
+#pragma unroll
+            for (int a = 0; a < BN / 64; ++a) tma_load_2d(sb + a * kAtomBytes, &tmB, &full_bar[stage], n0 + 64 * a, kb * UG_BK);
+          } else {
+            tma_load_2d(sb, &tmB, &full_bar[stage], kb * UG_BK, n0);
+          }
           if (++stage == kStages) { stage = 0; phase ^= 1u; }
         }
       }
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
-    constexpr uint32_t idesc = umma_idesc_bf16(UG_BM, BN);
+    constexpr uint32_t idesc = umma_idesc_bf16(UG_BM, BN, A_MN, B_MN);
     int stage = 0;
     uint32_t phase = 0;
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int64_t tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+    for (int64_t item = blockIdx.x; item < num_tiles; item += gridDim.x) {
+      const int split = (int)(item % splits);
+      const int kb0 = split * kb_per;
+      const int kb1 = (kb0 + kb_per < num_kb_total) ? kb0 + kb_per : num_kb_total;
       mbar_wait(&tempty_bar[acc], acc_phase ^ 1u);
       tc_fence_after();
       const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
-      for (int kb = 0; kb < num_kb; ++kb) {
+      for (int kb = kb0; kb < kb1; ++kb) {
         mbar_wait(&full_bar[stage], phase);
         tc_fence_after();
         if (elect_one()) {
           const uint32_t sa = smem_u32(stage_base + stage * Cfg::kStageBytes);
           const uint32_t sb = sa + Cfg::kStageBytesA;
-          const uint64_t da = umma_desc_k_sw128(sa);
-          const uint64_t db = umma_desc_k_sw128(sb);
+          const uint64_t da = A_MN ? umma_desc_mn_sw128(sa, kAtomBytes) : umma_desc_k_sw128(sa);
+          const uint64_t db = B_MN ? umma_desc_mn_sw128(sb, kAtomBytes) : umma_desc_k_sw128(sb);
+          // one UMMA consumes 16 k: K-major +32 bytes inside the 128-byte swizzle row (+2 in 16-byte
+          // units); MN-major +16 k-rows of 128 bytes = 2048 bytes (+128 units)
+          constexpr uint64_t ka = A_MN ? 128 : 2;
+          constexpr uint64_t kbs = B_MN ? 128 : 2;
 #pragma unroll
           for (int k = 0; k < UG_BK / 16; ++k) {
-            // advance 16 bf16 = 32 bytes inside the 128-byte swizzle row: +2 in 16-byte units
-            umma_bf16(d_tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc,
-                      (kb > 0 || k > 0) ? 1u : 0u);
+            umma_bf16(d_tmem, da + ka * (uint64_t)k, db + kbs * (uint64_t)k, idesc,
+                      (kb > kb0 || k > 0) ? 1u : 0u);
           }
           umma_commit(&empty_bar[stage]);
-          if (kb == num_kb - 1) umma_commit(&tfull_bar[acc]);
+          if (kb == kb1 - 1) umma_commit(&tfull_bar[acc]);
         }
         __syncwarp();
         if (++stage == kStages) { stage = 0; phase ^= 1u; }
@@ -259,9 +304,9 @@ umma_gemm_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     constexpr int kColsPerGroup = BN / Cfg::kColGroups;
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int64_t tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+    for (int64_t item = blockIdx.x; item < num_tiles; item += gridDim.x) {
       int64_t m_blk; int n_blk;
-      ug_tile_coords(tile, m_tiles, n_tiles, gm, m_blk, n_blk);
+      ug_tile_coords(item / splits, m_tiles, n_tiles, gm, m_blk, n_blk);
       const int64_t row = m_blk * UG_BM + q * 32 + lane;
       const bool row_ok = row < M;
       const int n0 = n_blk * BN + cg * kColsPerGroup;
