@@ -1,0 +1,289 @@
+"""GPU parity tests of the training path (loss forward + hand-written backward) through the C ABI.
+
+Reference: DiffLoss.forward / DiffActLoss.forward (DL:44-66, DAL:145-166) -> training_losses
+(GD:746-818) + autograd.  Checked against (i) the golden vectors produced by the unmodified reference
+(loss, dz, per-parameter gradient digests and samples), (ii) the CPU oracle's autograd on seeded inputs
+with ragged row counts, masks with zeros, t = 0 rows (decoder NLL branch) and the action-head shape.
+
+Tolerances: fp32 mode <= 1e-4 relative (max-norm per tensor, against the tensor's own max); bf16 mode:
+loss <= 1e-2 relative, gradients <= 4e-2 relative L2 per tensor (bf16 operands in forward and backward
+GEMMs, fp32 accumulation; the reference trains under bf16 autocast the same way).
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import uva_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+FP32_TOL = 1e-4
+BF16_LOSS_TOL = 1e-2
+BF16_GRAD_L2 = 4e-2
+
+
+def _cuda():
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    return torch.device("cuda", 0)
+
+
+def _T(a, dev=None):
+    t = torch.from_numpy(np.ascontiguousarray(a))
+    return t.to(dev) if dev is not None else t
+
+
+def _head(C, Z, W, D, params, mode, dev):
+    from unified_video_action_b200 import _lib
+
+    names = [n for n, _ in O.param_specs(C, Z, W, D)]
+    with torch.cuda.device(dev):
+        h = _lib.Head(C, Z, W, D, 1000, 100, mode)
+        h.load_weights([_T(params[n], dev) for n in names])
+    return h, names
+
+
+def _run(h, names, params, dev, target, z, mask, t, noise, dloss=1.0):
+    grads = [torch.zeros(params[n].shape, dtype=torch.float32, device=dev) for n in names]
+    m = None if mask is None else mask.to(dev)
+    loss, rows = h.loss_fwd(target.to(dev), z.to(dev), m, t.to(dev), noise.to(dev), want_rows=True)
+    dz = h.loss_bwd(torch.tensor([dloss], device=dev), target.to(dev), z.to(dev), m, t.to(dev), noise.to(dev), grads)
+    torch.cuda.synchronize()
+    return loss.cpu(), rows.cpu(), dz.cpu(), {n: g.cpu() for n, g in zip(names, grads)}
+
+
+def _oracle(P_np, target, z, mask, t, noise, act=False):
+    P = O.to_torch_params(P_np, requires_grad=True)
+    S = O.create_schedule("")
+    zz = z.clone().requires_grad_(True)
+    if act:
+        loss = O.diffactloss_forward(P, S, target, zz, t, noise)
+    else:
+        loss = O.diffloss_forward(P, S, target, zz, mask, t, noise)
+    loss.backward()
+    with torch.no_grad():
+        rows = O.training_losses(P, S, target, t, noise, z)["loss"]
+    return loss.detach(), rows, zz.grad, {k: p.grad for k, p in P.items()}
+
+
+def _check(mine, ref, mode, what):
+    mine, ref = mine.double(), ref.double()
+    scale = float(ref.abs().max())
+    if scale == 0.0:
+        assert float(mine.abs().max()) == 0.0, what
+        return
+    if mode == 0:
+        err = float((mine - ref).abs().max()) / scale
+        assert err <= FP32_TOL, (what, err)
+    else:
+        err = float((mine - ref).norm() / ref.norm())
+        assert err <= BF16_GRAD_L2, (what, err)
+
+
+@pytest.fixture(scope="module")
+def video(golden_dir):
+    dev = _cuda()
+    g = np.load(os.path.join(golden_dir, "video_head.npz"))
+    P = O.make_params(16, 768, 1024, 6, seed=1)
+    return dev, g, P
+
+
+@pytest.mark.parametrize("mode", [0, 1], ids=["fp32", "bf16"])
+def test_video_loss_and_grads_vs_reference_golden(video, mode):
+    """16 rows, masked mean: loss, dz and every parameter gradient against the unmodified reference."""
+    dev, g, P = video
+    h, names = _head(16, 768, 1024, 6, P, mode, dev)
+    loss, _, dz, grads = _run(h, names, P, dev, _T(g["tr_target"]).reshape(-1, 16), _T(g["tr_z"]).reshape(-1, 768),
+                              _T(g["tr_mask"]).reshape(-1), _T(g["tr_t"]), _T(g["tr_noise"]))
+    tol = FP32_TOL if mode == 0 else BF16_LOSS_TOL
+    assert abs(float(loss) - float(g["tr_loss"])) <= tol * abs(float(g["tr_loss"]))
+    _check(dz, _T(g["tr_dz"]).reshape(-1, 768), mode, "dz")
+    for k in names:
+        dg = g["tr_gdigest." + k]  # [sum, sum|.|, l2] of the reference gradient (float64)
+        f = grads[k].double().flatten()
+        rel = FP32_TOL * 10 if mode == 0 else BF16_GRAD_L2
+        assert abs(float(f.norm()) - dg[2]) <= rel * max(dg[2], 1e-12), (k, float(f.norm()), dg[2])
+        idx = _T(g["tr_gidx." + k])
+        ref = _T(g["tr_gsample." + k]).double()
+        err = float((f[idx] - ref).abs().max())
+        bound = (FP32_TOL if mode == 0 else BF16_GRAD_L2) * max(float(ref.abs().max()), dg[2] / max(1.0, f.numel() ** 0.5))
+        assert err <= 4 * bound, (k, err, bound)
+
+
+@pytest.mark.parametrize("mode", [0, 1], ids=["fp32", "bf16"])
+def test_t0_decoder_nll_rows_vs_reference_golden(video, mode):
+    """Rows with t = 0 take the discretised-Gaussian NLL branch (DU:47-73)."""
+    dev, g, P = video
+    h, names = _head(16, 768, 1024, 6, P, mode, dev)
+    x, t, nz, c = _T(g["t0_x"]), _T(g["t0_t"]), _T(g["t0_noise"]), _T(g["t0_c"])
+    _, rows, _, _ = _run(h, names, P, dev, x, c, None, t, nz)
+    tol = 2e-4 if mode == 0 else 2e-2
+    np.testing.assert_allclose(rows.numpy(), g["t0_loss"], rtol=tol, atol=tol * float(np.abs(g["t0_loss"]).max()))
+
+
+@pytest.mark.parametrize("mode", [0, 1], ids=["fp32", "bf16"])
+def test_ragged_masked_rows_vs_oracle(video, mode):
+    """333 rows (not a tile multiple), mask with zeros, t = 0 and t = 999 rows included."""
+    dev, _, P = video
+    gen = torch.Generator().manual_seed(11)
+    N = 333
+    target = torch.randn(N, 16, generator=gen) * 0.5
+    target[5, 3] = -1.2  # beyond the +-0.999 thresholds of the decoder NLL (DU:66-72)
+    target[6, 1] = 1.3
+    z = torch.randn(N, 768, generator=gen)
+    mask = (torch.rand(N, generator=gen) > 0.3).float()
+    t = torch.randint(0, 1000, (N,), generator=gen)
+    t[:12] = 0
+    t[12] = 999
+    noise = torch.randn(N, 16, generator=gen)
+    h, names = _head(16, 768, 1024, 6, P, mode, dev)
+    loss, rows, dz, grads = _run(h, names, P, dev, target, z, mask, t, noise, dloss=0.7)
+    rl, rr, rdz, rg = _oracle(P, target, z, mask, t, noise)
+    tol = FP32_TOL if mode == 0 else BF16_LOSS_TOL
+    assert abs(float(loss) - float(rl)) <= tol * abs(float(rl))
+    _check(rows, rr, mode, "row_loss")
+    _check(dz, 0.7 * rdz, mode, "dz")
+    for k in names:
+        _check(grads[k], 0.7 * rg[k], mode, k)
+
+
+@pytest.mark.parametrize("mode", [0, 1], ids=["fp32", "bf16"])
+def test_action_head_plain_mean_vs_oracle(golden_dir, mode):
+    """DiffActLoss shape: C = 2, 256 rows (PushT B=16), unmasked mean (DAL:162-164)."""
+    dev = _cuda()
+    P = O.make_params(2, 768, 1024, 6, seed=2)
+    gen = torch.Generator().manual_seed(5)
+    N = 256
+    target = torch.rand(N, 2, generator=gen) * 2 - 1
+    z = torch.randn(N, 768, generator=gen)
+    t = torch.randint(0, 1000, (N,), generator=gen)
+    noise = torch.randn(N, 2, generator=gen)
+    h, names = _head(2, 768, 1024, 6, P, mode, dev)
+    loss, rows, dz, grads = _run(h, names, P, dev, target, z, None, t, noise)
+    rl, rr, rdz, rg = _oracle(P, target, z, None, t, noise, act=True)
+    tol = FP32_TOL if mode == 0 else BF16_LOSS_TOL
+    assert abs(float(loss) - float(rl)) <= tol * abs(float(rl))
+    _check(dz, rdz, mode, "dz")
+    for k in names:
+        _check(grads[k], rg[k], mode, k)
+    g = np.load(os.path.join(golden_dir, "action_head.npz"))
+    h2, names2 = _head(2, 768, 1024, 6, P, mode, dev)
+    _, rows2, _, _ = _run(h2, names2, P, dev, _T(g["tr_target"]), _T(g["tr_z"]), None, _T(g["tr_t"]), _T(g["tr_noise"]))
+    rt = 2e-4 if mode == 0 else 2e-2
+    np.testing.assert_allclose(rows2.numpy(), g["tr_rowloss"], rtol=rt, atol=rt * float(np.abs(g["tr_rowloss"]).max()))
+
+
+def test_small_geometry_fp32_vs_oracle():
+    """Generic-width kernels (W = 64, depth 2, C = 3, Z = 32)."""
+    dev = _cuda()
+    C, Z, W, D = 3, 32, 64, 2
+    P = O.make_params(C, Z, W, D, seed=3)
+    gen = torch.Generator().manual_seed(8)
+    N = 70
+    target = torch.randn(N, C, generator=gen)
+    z = torch.randn(N, Z, generator=gen)
+    mask = (torch.rand(N, generator=gen) > 0.2).float()
+    t = torch.randint(0, 1000, (N,), generator=gen)
+    t[0] = 0
+    noise = torch.randn(N, C, generator=gen)
+    h, names = _head(C, Z, W, D, P, 0, dev)
+    loss, _, dz, grads = _run(h, names, P, dev, target, z, mask, t, noise)
+    rl, _, rdz, rg = _oracle(P, target, z, mask, t, noise)
+    assert abs(float(loss) - float(rl)) <= FP32_TOL * abs(float(rl))
+    _check(dz, rdz, 0, "dz")
+    for k in names:
+        _check(grads[k], rg[k], 0, k)
+
+
+@pytest.mark.parametrize("mode", [0, 1], ids=["fp32", "bf16"])
+def test_full_size_properties(video, mode):
+    """BASELINE size (PushT train, 16384 rows per GPU): size-independent properties.
+    (a) gradients are linear in dloss; (b) the backward ACCUMULATES into the gradient tensors;
+    (c) rows with mask = 0 contribute nothing: zeroing their inputs' influence leaves loss unchanged;
+    (d) the loss of a row permutation is the same."""
+    dev, _, P = video
+    N = 16384 if mode == 1 else 2048
+    gen = torch.Generator().manual_seed(21)
+    target = torch.randn(N, 16, generator=gen) * 0.5
+    z = torch.randn(N, 768, generator=gen)
+    mask = (torch.rand(N, generator=gen) > 0.25).float()
+    t = torch.randint(0, 1000, (N,), generator=gen)
+    noise = torch.randn(N, 16, generator=gen)
+    h, names = _head(16, 768, 1024, 6, P, mode, dev)
+    l1, rows1, dz1, g1 = _run(h, names, P, dev, target, z, mask, t, noise, dloss=1.0)
+    l2, _, dz2, g2 = _run(h, names, P, dev, target, z, mask, t, noise, dloss=2.0)
+    assert torch.isfinite(dz1).all() and float(l1) == float(l2)
+    rel = 1e-4 if mode == 0 else 2e-2  # split-K atomics reorder fp32 sums; bf16 rounds dnet-scaled operands
+    assert float((dz2 - 2 * dz1).norm() / (2 * dz1).norm()) <= rel
+    for k in names:
+        assert float((g2[k] - 2 * g1[k]).norm() / (2 * g1[k]).norm().clamp_min(1e-20)) <= rel, k
+    # masked-out rows: dz is exactly zero there, and the loss is the masked mean of the row losses
+    assert float(dz1[mask == 0].abs().max()) == 0.0
+    ref = float((rows1.double() * mask.double()).sum() / mask.double().sum())
+    assert abs(float(l1) - ref) <= 1e-5 * abs(ref)
+    # permutation invariance of the loss
+    perm = torch.randperm(N, generator=gen)
+    l3, _, _, _ = _run(h, names, P, dev, target[perm], z[perm], mask[perm], t[perm], noise[perm])
+    assert abs(float(l3) - float(l1)) <= 1e-5 * abs(float(l1))
+    # accumulate semantics
+    from unified_video_action_b200 import _lib  # noqa: F401
+
+    grads = [torch.zeros(P[n].shape, dtype=torch.float32, device=dev) for n in names]
+    args = (target.to(dev), z.to(dev), mask.to(dev), t.to(dev), noise.to(dev))
+    for _ in range(2):
+        h.loss_fwd(*args)
+        h.loss_bwd(torch.tensor([1.0], device=dev), *args, grads)
+    torch.cuda.synchronize()
+    for n, gacc in zip(names, grads):
+        assert float((gacc.cpu() - 2 * g1[n]).norm() / (2 * g1[n]).norm().clamp_min(1e-20)) <= rel, n
+
+
+def test_module_forward_backward_matches_oracle(video):
+    """The drop-in nn.Module: DiffLoss.forward under autograd with the reference's RNG call order
+    (randint for t, then randn_like for the noise; DL:51, GD:761)."""
+    dev, _, P = video
+    from unified_video_action_b200 import DiffLoss
+
+    head = DiffLoss(16, 768, 6, 1024, "100", n_frames=4, language_emb_model=None, language_emb_model_type=None,
+                    precision="fp32")
+    head.net.load_state_dict({k: _T(v) for k, v in P.items()})
+    head = head.to(dev)
+    gen = torch.Generator().manual_seed(3)
+    B, S = 3, 50
+    target = torch.randn(B, S, 16, generator=gen).to(dev)
+    z = torch.randn(B, S, 768, generator=gen).to(dev).requires_grad_(True)
+    mask = (torch.rand(B, S, generator=gen) > 0.3).float().to(dev)
+    torch.manual_seed(77)
+    loss = head(target, z, mask)
+    loss.backward()
+    torch.manual_seed(77)
+    t = torch.randint(0, 1000, (B * S,), device=dev)
+    noise = torch.randn(B * S, 16, device=dev)
+    rl, _, rdz, rg = _oracle(P, target.reshape(-1, 16).cpu(), z.detach().reshape(-1, 768).cpu(), mask.reshape(-1).cpu(),
+                             t.cpu(), noise.cpu())
+    assert loss.dim() == 0
+    assert abs(float(loss) - float(rl)) <= FP32_TOL * abs(float(rl))
+    _check(z.grad.reshape(-1, 768).cpu(), rdz, 0, "dz")
+    for k, p in head.net.named_parameters():
+        assert p.grad is not None, k
+        _check(p.grad.cpu(), rg[k], 0, k)
+
+
+def test_error_paths(video):
+    dev, _, P = video
+    from unified_video_action_b200 import _lib
+
+    h, names = _head(16, 768, 1024, 6, P, 1, dev)
+    x = torch.zeros(4, 16, device=dev)
+    z = torch.zeros(4, 768, device=dev)
+    t = torch.zeros(4, dtype=torch.int64, device=dev)
+    ws = torch.empty(1024, dtype=torch.uint8, device=dev)
+    loss = torch.empty(1, device=dev)
+    rc = _lib.lib().uva_head_loss_fwd(h._h, x.data_ptr(), z.data_ptr(), None, t.data_ptr(), x.data_ptr(), 4,
+                                      loss.data_ptr(), None, ws.data_ptr(), ws.numel(), None)
+    assert rc == -4 and b"workspace" in _lib.lib().uva_last_error()
+    rc = _lib.lib().uva_head_loss_fwd(h._h, None, z.data_ptr(), None, t.data_ptr(), x.data_ptr(), 4,
+                                      loss.data_ptr(), None, ws.data_ptr(), ws.numel(), None)
+    assert rc == -1

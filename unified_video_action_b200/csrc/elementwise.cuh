@@ -19,22 +19,6 @@ __global__ void k_pack_bf16(const float* __restrict__ src, bf16* __restrict__ ds
     dst[i] = (r < rows) ? __float2bfloat16_rn(src[i]) : __float2bfloat16_rn(0.f);
   }
 }
-// dst[k, r] (bf16, cols_pad x rows_pad... stored [cols x rows_pad]) = src[r, k]; zero for r >= rows.
-__global__ void k_pack_bf16_t(const float* __restrict__ src, bf16* __restrict__ dst, int rows,
-                              int rows_pad, int cols) {
-  __shared__ float tile[32][33];
-  const int r0 = blockIdx.y * 32, k0 = blockIdx.x * 32;
-  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
-    const int r = r0 + i, k = k0 + threadIdx.x;
-    tile[i][threadIdx.x] = (r < rows && k < cols) ? src[(int64_t)r * cols + k] : 0.f;
-  }
-  __syncthreads();
-  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
-    const int k = k0 + i, r = r0 + threadIdx.x;
-    if (k < cols && r < rows_pad) dst[(int64_t)k * rows_pad + r] = __float2bfloat16_rn(tile[threadIdx.x][i]);
-  }
-}
-
 template <typename TO>
 __global__ void k_convert(const float* __restrict__ src, TO* __restrict__ dst, int64_t n) {
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
@@ -42,24 +26,15 @@ __global__ void k_convert(const float* __restrict__ src, TO* __restrict__ dst, i
     dst[i] = from_f32<TO>(src[i]);
 }
 
-// SiLU in place on fp32 (time-embed hidden layer, DL:104-108)
-__global__ void k_silu_inplace(float* __restrict__ p, int64_t n) {
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
-       i += (int64_t)gridDim.x * blockDim.x) {
-    const float x = p[i];
-    p[i] = x / (1.0f + expf(-x));
-  }
-}
-
 // ------------------------------------------------------------------------------------------
 // ys = SiLU(cond_embed(c) + time_embed(t))   — first op of every adaLN_modulation (DL:158-160,
 // 181-183, 271-273).  temb is the [T_train, W] table; the timestep of row r is t_rows[r] when
-// t_rows != null, else t_all.   y_out (optional, fp32) keeps y for the backward.
+// t_rows != null, else t_all.   y_out (optional, TA) keeps y for the backward.
 // ------------------------------------------------------------------------------------------
 template <typename TA>
 __global__ void k_ysilu(const float* __restrict__ cemb, const float* __restrict__ temb,
                         const int64_t* __restrict__ t_rows, int t_all, TA* __restrict__ ys,
-                        float* __restrict__ y_out, int64_t rows, int W) {
+                        TA* __restrict__ y_out, int64_t rows, int W) {
   const int wq = W / 4;
   const int64_t n = rows * wq;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
@@ -70,8 +45,13 @@ __global__ void k_ysilu(const float* __restrict__ cemb, const float* __restrict_
     const float4 c = *reinterpret_cast<const float4*>(cemb + r * W + j);
     const float4 e = __ldg(reinterpret_cast<const float4*>(temb + t * W + j));
     float y[4] = {c.x + e.x, c.y + e.y, c.z + e.z, c.w + e.w};
-    if (y_out) *reinterpret_cast<float4*>(y_out + r * W + j) = make_float4(y[0], y[1], y[2], y[3]);
     TA o[4];
+    if (y_out) {
+#pragma unroll
+      for (int q = 0; q < 4; ++q) o[q] = from_f32<TA>(y[q]);
+      if constexpr (sizeof(TA) == 2) *reinterpret_cast<uint2*>(y_out + r * W + j) = *reinterpret_cast<uint2*>(o);
+      else *reinterpret_cast<float4*>(y_out + r * W + j) = *reinterpret_cast<float4*>(o);
+    }
 #pragma unroll
     for (int q = 0; q < 4; ++q) o[q] = from_f32<TA>(silu_f(y[q]));
     if constexpr (sizeof(TA) == 2) {

@@ -1,0 +1,340 @@
+// Backward-pass row kernels and reductions of the diffusion head (autograd of DL:261-283 written out
+// by hand).  TA = activation type of the arithmetic mode (float / bf16).
+#pragma once
+#include "common.cuh"
+
+namespace uva {
+
+// accurate SiLU derivative (fp32 time-embedding table path)
+__device__ __forceinline__ float dsilu_acc(float x) {
+  const float s = 1.0f / (1.0f + expf(-x));
+  return s * (1.0f + x * (1.0f - s));
+}
+
+template <typename TA>
+__device__ __forceinline__ void load4(const TA* p, float (&v)[4]);
+template <>
+__device__ __forceinline__ void load4<float>(const float* p, float (&v)[4]) {
+  const float4 t = *reinterpret_cast<const float4*>(p);
+  v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+}
+template <>
+__device__ __forceinline__ void load4<bf16>(const bf16* p, float (&v)[4]) {
+  const uint2 t = *reinterpret_cast<const uint2*>(p);
+  const __nv_bfloat162 a = *reinterpret_cast<const __nv_bfloat162*>(&t.x);
+  const __nv_bfloat162 b = *reinterpret_cast<const __nv_bfloat162*>(&t.y);
+  v[0] = __low2float(a); v[1] = __high2float(a); v[2] = __low2float(b); v[3] = __high2float(b);
+}
+__device__ __forceinline__ void store4(float* p, const float (&v)[4]) {
+  *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
+}
+__device__ __forceinline__ void store4(bf16* p, const float (&v)[4]) {
+  *reinterpret_cast<uint2*>(p) = make_uint2(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]));
+}
+
+// ------------------------------------------------------------------------------------------
+// FinalLayer.linear backward (DL:189): out[N,2C] = a_f[N,W] . Wl[2C,W]^T + bl, 2C <= 32: CUDA cores.
+//   da[r, j]  = sum_c dnet[r, c] Wl[c, j]                      (k_final_dgrad)
+//   dWl[c, j] += sum_r dnet[r, c] a_f[r, j],  dbl[c] += sum_r dnet[r, c]   (k_final_wgrad)
+// ------------------------------------------------------------------------------------------
+template <typename TA>
+__global__ void k_final_dgrad(const float* __restrict__ dnet, int ldn, const float* __restrict__ Wl,
+                              TA* __restrict__ da, int64_t rows, int W, int C2) {
+  const int wq = W / 4;
+  const int64_t n = rows * wq;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r = i / wq;
+    const int j = (int)(i - r * wq) * 4;
+    float acc[4] = {0.f, 0.f, 0.f, 0.f};
+    for (int c = 0; c < C2; ++c) {
+      const float d = dnet[r * ldn + c];
+      const float4 w = __ldg(reinterpret_cast<const float4*>(Wl + (int64_t)c * W + j));
+      acc[0] = fmaf(d, w.x, acc[0]); acc[1] = fmaf(d, w.y, acc[1]);
+      acc[2] = fmaf(d, w.z, acc[2]); acc[3] = fmaf(d, w.w, acc[3]);
+    }
+    store4(da + r * W + j, acc);
+  }
+}
+
+constexpr int FW_ROWS = 128;  // rows per block of the skinny weight-gradient kernels
+template <typename TA>
+__global__ void __launch_bounds__(256)
+k_final_wgrad(const float* __restrict__ dnet, int ldn, const TA* __restrict__ a, float* __restrict__ dWl,
+              float* __restrict__ dbl, int64_t rows, int W, int C2) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t r0 = (int64_t)blockIdx.y * FW_ROWS;
+  const int64_t r1 = (r0 + FW_ROWS < rows) ? r0 + FW_ROWS : rows;
+  float acc[32];
+#pragma unroll
+  for (int c = 0; c < 32; ++c) acc[c] = 0.f;
+  if (j < W) {
+    for (int64_t r = r0; r < r1; ++r) {
+      const float av = to_f32(a[r * W + j]);
+#pragma unroll
+      for (int c = 0; c < 32; ++c)
+        if (c < C2) acc[c] = fmaf(dnet[r * ldn + c], av, acc[c]);
+    }
+#pragma unroll
+    for (int c = 0; c < 32; ++c)
+      if (c < C2 && dWl) atomicAdd(dWl + (int64_t)c * W + j, acc[c]);
+  }
+  if (blockIdx.x == 0 && threadIdx.x < C2 && dbl) {
+    float s = 0.f;
+    for (int64_t r = r0; r < r1; ++r) s += dnet[r * ldn + threadIdx.x];
+    atomicAdd(dbl + threadIdx.x, s);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// input_proj backward (DL:268): h0 = x_t . Wi^T + bi with K = C <= 16:
+//   dWi[j, c] += sum_r dh[r, j] x_t[r, c],  dbi[j] += sum_r dh[r, j].
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+k_inproj_wgrad(const float* __restrict__ dh, const float* __restrict__ xt, float* __restrict__ dWi,
+               float* __restrict__ dbi, int64_t rows, int W, int C) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t r0 = (int64_t)blockIdx.y * FW_ROWS;
+  const int64_t r1 = (r0 + FW_ROWS < rows) ? r0 + FW_ROWS : rows;
+  if (j >= W) return;
+  float acc[16];
+#pragma unroll
+  for (int c = 0; c < 16; ++c) acc[c] = 0.f;
+  float sb = 0.f;
+  for (int64_t r = r0; r < r1; ++r) {
+    const float d = dh[r * W + j];
+    sb += d;
+#pragma unroll
+    for (int c = 0; c < 16; ++c)
+      if (c < C) acc[c] = fmaf(d, xt[r * C + c], acc[c]);
+  }
+  if (dWi) {
+#pragma unroll
+    for (int c = 0; c < 16; ++c)
+      if (c < C) atomicAdd(dWi + (int64_t)j * C + c, acc[c]);
+  }
+  if (dbi) atomicAdd(dbi + j, sb);
+}
+
+// ------------------------------------------------------------------------------------------
+// Gated residual backward (DL:167: h' = h + gate * q):  dq = dh * gate, dgate = dh * q.
+// dh itself passes through unchanged (residual).  gate / dgate live in the modulation buffers.
+// ------------------------------------------------------------------------------------------
+template <typename TA>
+__global__ void k_gate_bwd(const float* __restrict__ dh, const TA* __restrict__ gate, const TA* __restrict__ q,
+                           int64_t ldmod, TA* __restrict__ dq, TA* __restrict__ dgate, int64_t rows, int W) {
+  const int wq = W / 4;
+  const int64_t n = rows * wq;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r = i / wq;
+    const int j = (int)(i - r * wq) * 4;
+    const float4 d = *reinterpret_cast<const float4*>(dh + r * W + j);
+    float g[4], qq[4];
+    load4<TA>(gate + r * ldmod + j, g);
+    load4<TA>(q + r * W + j, qq);
+    const float o1[4] = {d.x * g[0], d.y * g[1], d.z * g[2], d.w * g[3]};
+    const float o2[4] = {d.x * qq[0], d.y * qq[1], d.z * qq[2], d.w * qq[3]};
+    store4(dq + r * W + j, o1);
+    store4(dgate + r * ldmod + j, o2);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// Backward of a = LN(h)[* ln_w + ln_b] * (1 + scale) + shift  (modulate DL:93-94 on in_ln / norm_final):
+//   dshift = da, dscale = da * nhat, dnhat = da * (1 + scale), dln_w += sum_r dnhat * xhat,
+//   dln_b += sum_r dnhat, dxhat = dnhat * ln_w, dh_ln = rstd (dxhat - mean(dxhat) - xhat mean(dxhat xhat)).
+// dh = (first ? 0 : dh) + dh_ln.  One warp per row, W = NV * 128; the column sums for ln_w / ln_b are
+// kept in registers over the rows of a warp, combined through shared memory and added atomically.
+// ------------------------------------------------------------------------------------------
+template <typename TA, int NV>
+__global__ void __launch_bounds__(256)
+k_lnmod_bwd(const TA* __restrict__ da, const float* __restrict__ h, const float* __restrict__ stats,
+            const float* __restrict__ ln_w, const float* __restrict__ ln_b, const TA* __restrict__ scale,
+            int64_t ldmod, TA* __restrict__ dshift, TA* __restrict__ dscale, float* __restrict__ dh, int first,
+            float* __restrict__ dln_w, float* __restrict__ dln_b, int64_t rows) {
+  constexpr int W = NV * 128;
+  __shared__ float red[8][W / 4 + 1];  // reused for the two column sums (quarter of the row at a time)
+  const int lane = threadIdx.x & 31;
+  const int wib = threadIdx.x >> 5;
+  const int64_t warp_global = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t warps_total = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  float aw[NV][4], ab[NV][4];
+#pragma unroll
+  for (int i = 0; i < NV; ++i)
+#pragma unroll
+    for (int q = 0; q < 4; ++q) aw[i][q] = ab[i][q] = 0.f;
+
+  for (int64_t r = warp_global; r < rows; r += warps_total) {
+    const float mean = stats[2 * r], rstd = stats[2 * r + 1];
+    float xh[NV][4], dx[NV][4];
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int j = (lane + 32 * i) * 4;
+      const float4 hv = *reinterpret_cast<const float4*>(h + r * W + j);
+      float d[4], sc[4];
+      load4<TA>(da + r * W + j, d);
+      load4<TA>(scale + r * ldmod + j, sc);
+      xh[i][0] = (hv.x - mean) * rstd; xh[i][1] = (hv.y - mean) * rstd;
+      xh[i][2] = (hv.z - mean) * rstd; xh[i][3] = (hv.w - mean) * rstd;
+      float lw[4] = {1.f, 1.f, 1.f, 1.f}, lb[4] = {0.f, 0.f, 0.f, 0.f};
+      if (ln_w) {
+        const float4 g = __ldg(reinterpret_cast<const float4*>(ln_w + j));
+        const float4 b = __ldg(reinterpret_cast<const float4*>(ln_b + j));
+        lw[0] = g.x; lw[1] = g.y; lw[2] = g.z; lw[3] = g.w;
+        lb[0] = b.x; lb[1] = b.y; lb[2] = b.z; lb[3] = b.w;
+      }
+      float dsc[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const float nh = xh[i][q] * lw[q] + lb[q];
+        dsc[q] = d[q] * nh;
+        const float dn = d[q] * (1.0f + sc[q]);
+        aw[i][q] += dn * xh[i][q];
+        ab[i][q] += dn;
+        dx[i][q] = dn * lw[q];
+        s1 += dx[i][q];
+        s2 += dx[i][q] * xh[i][q];
+      }
+      store4(dshift + r * ldmod + j, d);
+      store4(dscale + r * ldmod + j, dsc);
+    }
+    s1 = warp_sum(s1) * (1.0f / W);
+    s2 = warp_sum(s2) * (1.0f / W);
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int j = (lane + 32 * i) * 4;
+      float o[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) o[q] = rstd * (dx[i][q] - s1 - xh[i][q] * s2);
+      if (!first) {
+        const float4 p = *reinterpret_cast<const float4*>(dh + r * W + j);
+        o[0] += p.x; o[1] += p.y; o[2] += p.z; o[3] += p.w;
+      }
+      store4(dh + r * W + j, o);
+    }
+  }
+  if (dln_w == nullptr) return;  // uniform over the grid
+  // block-level column sums: 8 warps -> shared -> atomics, a quarter of the row (W/4 columns) per pass
+  for (int which = 0; which < 2; ++which) {
+    for (int part = 0; part < 4; ++part) {
+      __syncthreads();
+#pragma unroll
+      for (int i = 0; i < NV; ++i) {
+        const int j = (lane + 32 * i) * 4;
+        if (j / (W / 4) == part) {
+#pragma unroll
+          for (int q = 0; q < 4; ++q) red[wib][j - part * (W / 4) + q] = which ? ab[i][q] : aw[i][q];
+        }
+      }
+      __syncthreads();
+      for (int c = threadIdx.x; c < W / 4; c += blockDim.x) {
+        float s = 0.f;
+#pragma unroll
+        for (int w8 = 0; w8 < 8; ++w8) s += red[w8][c];
+        atomicAdd((which ? dln_b : dln_w) + part * (W / 4) + c, s);
+      }
+    }
+  }
+}
+
+// generic width (test geometries): one warp per row, no register caching, column sums by atomics
+template <typename TA>
+__global__ void __launch_bounds__(256)
+k_lnmod_bwd_generic(const TA* __restrict__ da, const float* __restrict__ h, const float* __restrict__ stats,
+                    const float* __restrict__ ln_w, const float* __restrict__ ln_b, const TA* __restrict__ scale,
+                    int64_t ldmod, TA* __restrict__ dshift, TA* __restrict__ dscale, float* __restrict__ dh,
+                    int first, float* __restrict__ dln_w, float* __restrict__ dln_b, int64_t rows, int W) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp_global = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t warps_total = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  for (int64_t r = warp_global; r < rows; r += warps_total) {
+    const float mean = stats[2 * r], rstd = stats[2 * r + 1];
+    float s1 = 0.f, s2 = 0.f;
+    for (int j = lane; j < W; j += 32) {
+      const float xh = (h[r * W + j] - mean) * rstd;
+      const float d = to_f32(da[r * W + j]);
+      const float lw = ln_w ? ln_w[j] : 1.f, lb = ln_w ? ln_b[j] : 0.f;
+      const float dn = d * (1.0f + to_f32(scale[r * ldmod + j]));
+      dshift[r * ldmod + j] = from_f32<TA>(d);
+      dscale[r * ldmod + j] = from_f32<TA>(d * (xh * lw + lb));
+      if (dln_w) {
+        atomicAdd(dln_w + j, dn * xh);
+        atomicAdd(dln_b + j, dn);
+      }
+      s1 += dn * lw;
+      s2 += dn * lw * xh;
+    }
+    s1 = warp_sum(s1) / (float)W;
+    s2 = warp_sum(s2) / (float)W;
+    for (int j = lane; j < W; j += 32) {
+      const float xh = (h[r * W + j] - mean) * rstd;
+      const float lw = ln_w ? ln_w[j] : 1.f;
+      const float dn = to_f32(da[r * W + j]) * (1.0f + to_f32(scale[r * ldmod + j]));
+      const float o = rstd * (dn * lw - s1 - xh * s2);
+      dh[r * W + j] = (first ? 0.f : dh[r * W + j]) + o;
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// Column sums (bias gradients): out[c] += sum_r X[r, c].  Block = 32 column quads x 8 row lanes,
+// FW_ROWS*4 rows per block.
+// ------------------------------------------------------------------------------------------
+template <typename TI>
+__global__ void __launch_bounds__(256)
+k_colsum(const TI* __restrict__ X, int64_t ld, int64_t rows, int cols, float* __restrict__ out) {
+  __shared__ float red[8][128 + 4];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int c0 = (blockIdx.x * 32 + tx) * 4;
+  const int64_t r0 = (int64_t)blockIdx.y * (FW_ROWS * 4);
+  const int64_t r1 = (r0 + FW_ROWS * 4 < rows) ? r0 + FW_ROWS * 4 : rows;
+  float s[4] = {0.f, 0.f, 0.f, 0.f};
+  if (c0 < cols) {
+    for (int64_t r = r0 + ty; r < r1; r += 8) {
+      float v[4];
+      load4<TI>(X + r * ld + c0, v);
+      s[0] += v[0]; s[1] += v[1]; s[2] += v[2]; s[3] += v[3];
+    }
+  }
+#pragma unroll
+  for (int q = 0; q < 4; ++q) red[ty][tx * 4 + q] = s[q];
+  __syncthreads();
+  if (threadIdx.x < 128) {
+    const int c = blockIdx.x * 128 + threadIdx.x;
+    if (c < cols) {
+      float t = 0.f;
+#pragma unroll
+      for (int w8 = 0; w8 < 8; ++w8) t += red[w8][threadIdx.x];
+      atomicAdd(out + c, t);
+    }
+  }
+}
+
+// dtemb[t[r], :] += dy[r, :]   (gradient of the time-embedding table rows gathered in y = c + temb[t])
+template <typename TA>
+__global__ void k_temb_scatter(const TA* __restrict__ dy, const int64_t* __restrict__ t,
+                               float* __restrict__ dtemb, int64_t rows, int W) {
+  const int wq = W / 4;
+  const int64_t n = rows * wq;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r = i / wq;
+    const int j = (int)(i - r * wq) * 4;
+    float v[4];
+    load4<TA>(dy + r * W + j, v);
+    red_add_v4(dtemb + t[r] * W + j, v[0], v[1], v[2], v[3]);
+  }
+}
+
+// out = SiLU(in) (fp32, accurate exp) and dpre = dhid * SiLU'(pre): time-embedding MLP table
+__global__ void k_silu_f32(const float* __restrict__ in, float* __restrict__ out, int64_t n) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const float x = in[i];
+    out[i] = x / (1.0f + expf(-x));
+  }
+}
+__global__ void k_dsilu_mul(float* __restrict__ d, const float* __restrict__ pre, int64_t n) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    d[i] *= dsilu_acc(pre[i]);
+}
+
+}  // namespace uva

@@ -16,6 +16,7 @@
 #include "epilogue.cuh"
 #include "schedule.hpp"
 #include "sgemm.cuh"
+#include "train_bwd_kernels.cuh"
 #include "train_kernels.cuh"
 #include "umma_gemm.cuh"
 
@@ -142,6 +143,7 @@ struct UvaHead {
   float* feat = nullptr;      // [T_train, 256] sinusoidal features (DL:110-134)
   float* temb = nullptr;      // [T_train, W] TimestepEmbedder(t) table
   float* temb_hidden = nullptr;  // [T_train, W] SiLU(Linear0(feat)) (kept for the backward)
+  float* temb_pre = nullptr;     // [T_train, W] Linear0(feat) before the SiLU (kept for the backward)
   // fp32 parameter copy, own layout (offsets in floats)
   float* wf = nullptr;
   size_t wf_floats = 0;
@@ -152,9 +154,6 @@ struct UvaHead {
   size_t wb_elems = 0;
   size_t ob_condw, ob_adaw, ob_linw;      // [W,Z], [nmod,W], [32,W] (zero padded)
   std::vector<size_t> ob_w1, ob_w2;       // [W,W]
-  // transposed bf16 copies for dgrad: W^T stored [K_in, N_out]
-  size_t ob_condw_t, ob_adaw_t, ob_linw_t;  // [Z,W], [W,nmod], [W,32]
-  std::vector<size_t> ob_w1_t, ob_w2_t;
   bool weights_loaded = false;
   int64_t launches = 0;
   PFN_encodeTiled encode = nullptr;
@@ -286,6 +285,7 @@ extern "C" int uva_head_create(const UvaHeadDesc* desc, UvaHead** out) {
     CUDA_TRY(cudaMemcpy(h->feat, f.data(), f.size() * sizeof(float), cudaMemcpyHostToDevice));
     CUDA_TRY(cudaMalloc(&h->temb, (size_t)d.T_train * d.W * sizeof(float)));
     CUDA_TRY(cudaMalloc(&h->temb_hidden, (size_t)d.T_train * d.W * sizeof(float)));
+    CUDA_TRY(cudaMalloc(&h->temb_pre, (size_t)d.T_train * d.W * sizeof(float)));
   }
 
   // fp32 parameter layout
@@ -311,10 +311,8 @@ extern "C" int uva_head_create(const UvaHeadDesc* desc, UvaHead** out) {
     size_t o = 0;
     auto take = [&](size_t n) { size_t r = o; o += (n + 511) / 512 * 512; return r; };
     h->ob_condw = take(W * Z); h->ob_adaw = take((size_t)h->nmod * W); h->ob_linw = take(32 * W);
-    h->ob_condw_t = take(Z * W); h->ob_adaw_t = take((size_t)W * h->nmod); h->ob_linw_t = take(W * 32);
     for (int b = 0; b < d.depth; ++b) {
       h->ob_w1.push_back(take(W * W)); h->ob_w2.push_back(take(W * W));
-      h->ob_w1_t.push_back(take(W * W)); h->ob_w2_t.push_back(take(W * W));
     }
     h->wb_elems = o;
     CUDA_TRY(cudaMalloc(&h->wb, o * sizeof(bf16)));
@@ -331,7 +329,7 @@ extern "C" int uva_head_create(const UvaHeadDesc* desc, UvaHead** out) {
 
 extern "C" void uva_head_destroy(UvaHead* h) {
   if (!h) return;
-  cudaFree(h->d_tables); cudaFree(h->feat); cudaFree(h->temb); cudaFree(h->temb_hidden);
+  cudaFree(h->d_tables); cudaFree(h->feat); cudaFree(h->temb); cudaFree(h->temb_hidden); cudaFree(h->temb_pre);
   cudaFree(h->wf); cudaFree(h->wb);
   if (h->side) cudaStreamDestroy(h->side);
   if (h->ev_fork) cudaEventDestroy(h->ev_fork);
