@@ -138,6 +138,30 @@ def test_umma_gemm_wgrad_layout(M, N, K):
     assert err <= 3e-4 * float(ref.abs().max()), err
 
 
+@pytest.mark.parametrize("layout,M,N,K", [
+    (8, 256, 256, 64), (8, 300, 512, 1024), (8, 4101, 1024, 1024), (8, 129, 256, 128), (8, 20000, 3072, 256),
+    (9, 300, 768, 1024), (9, 4101, 1024, 3072), (9, 512, 256, 200),
+    (10, 256, 256, 64), (10, 1024, 1024, 16384), (10, 3072, 768, 5000), (10, 200, 256, 130),
+])
+def test_umma_pair_gemm_layouts(layout, M, N, K):
+    """CTA-pair (cta_group::2) kernel, 256 x 256 tiles: forward, data-gradient and weight-gradient forms."""
+    dev = _cuda()
+    from unified_video_action_b200 import _lib
+
+    g = torch.Generator(device="cpu").manual_seed(layout * 1000 + M + N + K)
+    form = layout & 7
+    A = torch.randn((K, M) if form == 2 else (M, K), generator=g).to(dev).bfloat16()
+    B = (torch.randn((N, K) if form == 0 else (K, N), generator=g) / K ** 0.5).to(dev).bfloat16()
+    bias = None if form == 2 else torch.randn(N, generator=g).to(dev)
+    D = _lib.gemm_bf16_selftest(A, B, bias, 256, layout=layout)
+    Af = A.float().t() if form == 2 else A.float()
+    Bf = B.float().t() if form == 0 else B.float()
+    ref = Af @ Bf + (0 if bias is None else bias)
+    torch.cuda.synchronize()
+    err = float((D - ref).abs().max())
+    assert err <= 3e-4 * float(ref.abs().max()), err
+
+
 # ------------------------------------------------------------------------------------------
 # SimpleMLPAdaLN.forward (DL:261-283)
 # ------------------------------------------------------------------------------------------

@@ -19,6 +19,25 @@ __global__ void k_pack_bf16(const float* __restrict__ src, bf16* __restrict__ ds
     dst[i] = (r < rows) ? __float2bfloat16_rn(src[i]) : __float2bfloat16_rn(0.f);
   }
 }
+// AdaLN modulation weight of one block ([nrow = 3W or 2W, W] fp32: shift | scale | gate rows) -> bf16 in
+// tile order for the fused LayerNorm-modulate epilogue: 256-row tiles of (128 shift rows | the matching
+// 128 scale rows), then the gate rows unchanged.  The bias gets the same permutation (fp32).
+__global__ void k_pack_ada_perm(const float* __restrict__ src, const float* __restrict__ bsrc,
+                                bf16* __restrict__ dst, float* __restrict__ bdst, int nrow, int W) {
+  const int64_t n = (int64_t)nrow * W;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int r = (int)(i / W);
+    const int k = (int)(i - (int64_t)r * W);
+    int sr = r;
+    if (r < 2 * W) {
+      const int j = r / 256, w = r % 256;
+      sr = (w < 128) ? j * 128 + w : W + j * 128 + (w - 128);
+    }
+    dst[i] = __float2bfloat16_rn(src[(int64_t)sr * W + k]);
+    if (k == 0) bdst[r] = bsrc[sr];
+  }
+}
+
 template <typename TO>
 __global__ void k_convert(const float* __restrict__ src, TO* __restrict__ dst, int64_t n) {
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
@@ -68,10 +87,10 @@ __global__ void k_ysilu(const float* __restrict__ cemb, const float* __restrict_
 // x[r % half] (forward_with_cfg, DL:286-287).  One block = 32 rows x W columns; each thread keeps
 // the weights of 4 output columns in registers.
 // ------------------------------------------------------------------------------------------
-constexpr int IP_ROWS = 32;
+constexpr int IP_ROWS = 64;
 __global__ void __launch_bounds__(256)
 k_input_proj(const float* __restrict__ x, const float* __restrict__ Wi, const float* __restrict__ bi,
-             float* __restrict__ h, int64_t rows, int C, int W, int64_t half) {
+             float* __restrict__ h, int64_t rows, int C, int W, int64_t half, float* __restrict__ stats) {
   const int64_t r0 = (int64_t)blockIdx.x * IP_ROWS;
   for (int j0 = threadIdx.x * 4; j0 < W; j0 += blockDim.x * 4) {
     float w[4][16];
@@ -79,10 +98,19 @@ k_input_proj(const float* __restrict__ x, const float* __restrict__ Wi, const fl
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
       b[q] = bi[j0 + q];
+      if (C == 16) {  // 4 x 16-byte loads per output column
+        const float4* wp = reinterpret_cast<const float4*>(Wi + (int64_t)(j0 + q) * 16);
 #pragma unroll
-      for (int c = 0; c < 16; ++c) w[q][c] = (c < C) ? Wi[(int64_t)(j0 + q) * C + c] : 0.f;
+        for (int c4 = 0; c4 < 4; ++c4) {
+          const float4 t = __ldg(wp + c4);
+          w[q][4 * c4] = t.x; w[q][4 * c4 + 1] = t.y; w[q][4 * c4 + 2] = t.z; w[q][4 * c4 + 3] = t.w;
+        }
+      } else {
+#pragma unroll
+        for (int c = 0; c < 16; ++c) w[q][c] = (c < C) ? Wi[(int64_t)(j0 + q) * C + c] : 0.f;
+      }
     }
-#pragma unroll 2
+#pragma unroll 4
     for (int rr = 0; rr < IP_ROWS; ++rr) {
       const int64_t r = r0 + rr;
       if (r >= rows) break;
@@ -106,6 +134,12 @@ k_input_proj(const float* __restrict__ x, const float* __restrict__ Wi, const fl
         for (int q = 0; q < 4; ++q) acc[q] = fmaf(xv[c], w[q][c], acc[q]);
       }
       *reinterpret_cast<float4*>(h + r * W + j0) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+      if (stats != nullptr) {  // row sums for the LayerNorm of the first block (uniform branch)
+        const float s = warp_sum((acc[0] + acc[1]) + (acc[2] + acc[3]));
+        const float ss = warp_sum((acc[0] * acc[0] + acc[1] * acc[1]) + (acc[2] * acc[2] + acc[3] * acc[3]));
+        // one (sum, sum of squares) slot per 128 columns = per warp (deterministic, no atomics)
+        if ((threadIdx.x & 31) == 0) *reinterpret_cast<float2*>(stats + (r * (W / 128) + j0 / 128) * 2) = make_float2(s, ss);
+      }
     }
   }
 }

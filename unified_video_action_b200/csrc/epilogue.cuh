@@ -18,6 +18,13 @@ struct EpiArgs {
   const float* res = nullptr;   // residual input of the gated-residual kinds (row stride ldo); null = out
   int32_t n_valid = 0;          // valid output columns (columns >= n_valid are padding)
   float alpha = 1.0f;
+  // LayerNorm coupling (bf16 sampling path): the gated-residual kinds add the row sums (sum, sum of
+  // squares) of their output to stats[row][2]; EPI_LNMOD reads them back (see umma_gemm2.cuh)
+  float* stats = nullptr;
+  const float* ln_w = nullptr;  // [W] LayerNorm affine (null: none)
+  const float* ln_b = nullptr;
+  int32_t ln_tiles = 0;         // EPI_LNMOD: number of leading 256-column tiles that are (shift | scale) pairs
+  int32_t ln_width = 0;         // EPI_LNMOD: W
 };
 
 enum EpiKind {
@@ -30,6 +37,9 @@ enum EpiKind {
   EPI_DSILU_ACT = 6,  // out(TA)[r,c]   = (acc) * SiLU'(aux(TA)[r,c])            (dgrad through SiLU)
   EPI_ATOMIC_F32 = 7, // atomicAdd(out(f32)[r,c], alpha * acc)                   (split-K wgrad)
   EPI_GATED_SAVE = 8, // q = acc + bias; out2(TA) = q; out(f32) = res + aux * q  (training fwd, DL:167)
+  EPI_LNMOD = 9,      // AdaLN GEMM with the LayerNorm-modulate fused (CTA-pair kernel only): tiles < ln_tiles
+                      // hold 128 shift | 128 scale columns -> out(TA) = LN(res)[*ln_w+ln_b]*(1+scale)+shift;
+                      // the other tiles (gate) are stored to out2(TA)                         (DL:93-94, 163-166)
 };
 
 template <int KIND, typename TA>

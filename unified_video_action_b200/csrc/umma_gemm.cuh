@@ -59,7 +59,18 @@ struct RowEpi {
   struct Pre {
     float4 h[8];
     uint4 g[4];
+    float s = 0.f, ss = 0.f;  // row sums of the outputs written so far (LayerNorm statistics)
   };
+  // after the last chunk of a tile: publish the row sums
+  __device__ static __forceinline__ void finish(const EpiArgs& e, int64_t row, Pre& p) {
+    if constexpr (KIND == EPI_GATED_RES || KIND == EPI_GATED_SAVE) {
+      if (e.stats != nullptr) {
+        atomicAdd(e.stats + 2 * row, p.s);
+        atomicAdd(e.stats + 2 * row + 1, p.ss);
+        p.s = p.ss = 0.f;
+      }
+    }
+  }
 
   __device__ static __forceinline__ void prefetch(const EpiArgs& e, int64_t row, int col0, Pre& p) {
     if constexpr (KIND == EPI_GATED_RES || KIND == EPI_GATED_SAVE) {
@@ -85,7 +96,7 @@ struct RowEpi {
     }
   }
 
-  __device__ static __forceinline__ void store(const EpiArgs& e, int64_t row, int col0, const uint32_t (&v)[32], const Pre& p) {
+  __device__ static __forceinline__ void store(const EpiArgs& e, int64_t row, int col0, const uint32_t (&v)[32], Pre& p) {
     constexpr bool kVec = (sizeof(TA) == 2) || KIND == EPI_STORE_F32;  // (gated kinds: TA is bf16 here)
     if constexpr (KIND == EPI_ATOMIC_F32) {
       if (col0 + 32 <= e.n_valid) {
@@ -133,6 +144,8 @@ struct RowEpi {
         r.z = fmaf(gb.x, __uint_as_float(v[4 * i + 2]) + b[4 * i + 2], r.z);
         r.w = fmaf(gb.y, __uint_as_float(v[4 * i + 3]) + b[4 * i + 3], r.w);
         o[i] = r;
+        p.s += (r.x + r.y) + (r.z + r.w);
+        p.ss += (r.x * r.x + r.y * r.y) + (r.z * r.z + r.w * r.w);
       }
     } else {
       // 16-bit outputs: out = f(acc + bias) packed to bf16, 4 x 16-byte stores
@@ -327,6 +340,7 @@ umma_gemm_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tempty_bar[acc]);
+      if (row_ok) RowEpi<KIND, TA>::finish(ep, row, pre);
       if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
     }
   }

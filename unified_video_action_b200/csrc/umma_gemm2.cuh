@@ -1,0 +1,341 @@
+// CTA-pair tcgen05 GEMM (sm_100a, cta_group::2): D[M,N] = sum_k A(m,k) B(n,k), bf16 operands, fp32
+// accumulation in tensor memory, fused row-segment epilogue (RowEpi of umma_gemm.cuh).
+//
+// A cluster of two CTAs (one TPC) owns a 256 x 256 output tile: CTA r loads the A rows
+// [256 m_blk + 128 r, +128) and the B rows [256 n_blk + 128 r, +128) of every k-block, the leader CTA
+// issues ONE tcgen05.mma.cta_group::2 (M = 256, N = 256, K = 16) per 16 k that reads A from each
+// CTA's own shared memory and the two B halves from both, and each CTA's tensor memory receives
+// the accumulators of its own 128 rows.  Per SM and per 128 tensor-pipe cycles that is 8 KB of shared
+// memory operand reads instead of the 12 KB of the single-CTA 128 x 256 tile, and half the L2 -> SMEM
+// traffic for B.
+//
+//   warp 0 : TMA producer (both CTAs; completion bytes of both land on the LEADER's full barrier)
+//   warp 1 : MMA issuer (leader CTA only); tcgen05.commit multicasts to the barriers of both CTAs
+//   warp 2 : tensor-memory allocator (cta_group::2 allocation, both CTAs)
+//   warps 4-11: epilogue of this CTA's 128 rows; accumulator stage release = remote arrive on the
+//           leader's barrier (16 arrivals: 8 warps x 2 CTAs)
+#pragma once
+#include "pair_epilogue.cuh"
+#include "umma_gemm.cuh"
+
+namespace uva {
+
+template <int BN>
+struct Umma2Cfg {
+  static constexpr int kBNH = BN / 2;  // B rows per CTA
+  static constexpr int kStageBytesA = UG_BM * UG_BK * 2;
+  static constexpr int kStageBytesB = kBNH * UG_BK * 2;
+  static constexpr int kStageBytes = kStageBytesA + kStageBytesB;
+  static constexpr int kStages = 5;
+  static constexpr int kBarBytes = 256;
+  static constexpr int kSmemBytes = 1024 + kStages * kStageBytes + kBarBytes + 8 * PE_WARP_BYTES;  // + epilogue staging
+  static constexpr uint32_t kTmemCols = 512;  // 2 accumulator stages x 256 columns
+};
+
+template <int BN, int KIND, typename TA, bool A_MN = false, bool B_MN = false>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(UG_THREADS, 1)
+umma_gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                  int64_t M, int N, int K, int gm, int splits, EpiArgs ep) {
+  static_assert(BN == 256, "CTA-pair kernel: 256 x 256 tiles");
+  using Cfg = Umma2Cfg<BN>;
+  constexpr int kStages = Cfg::kStages;
+  constexpr int BM2 = 2 * UG_BM;
+  constexpr uint32_t kAtomBytes = 64 * UG_BK * 2;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* stage_base = smem;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kStages * Cfg::kStageBytes);
+  uint64_t* full_bar = bars;                      // [kStages] (used in the leader CTA)
+  uint64_t* empty_bar = bars + kStages;           // [kStages] (each CTA its own, multicast commit)
+  uint64_t* tfull_bar = bars + 2 * kStages;       // [2]       (each CTA its own, multicast commit)
+  uint64_t* tempty_bar = bars + 2 * kStages + 2;  // [2]       (used in the leader CTA)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 4);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const bool leader = rank == 0;
+  const int64_t cluster_id = blockIdx.x >> 1;
+  const int64_t num_clusters = gridDim.x >> 1;
+  const int64_t m_tiles = (M + BM2 - 1) / BM2;
+  const int n_tiles = N / BN;
+  const int64_t num_items = m_tiles * n_tiles * splits;
+  const int num_kb_total = (K + UG_BK - 1) / UG_BK;
+  const int kb_per = (num_kb_total + splits - 1) / splits;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&tfull_bar[s], 1);
+      mbar_init(&tempty_bar[s], 16);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 2) tmem_alloc_2sm<Cfg::kTmemCols>(tmem_slot);
+  tc_fence_before();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================== TMA producer (both CTAs) =====================
+    if (elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int64_t item = cluster_id; item < num_items; item += num_clusters) {
+        int64_t m_blk; int n_blk;
+        const int64_t tile = item / splits;
+        const int split = (int)(item - tile * splits);
+        ug_tile_coords(tile, m_tiles, n_tiles, gm, m_blk, n_blk);
+        const int32_t m0 = (int32_t)(m_blk * BM2) + (int32_t)rank * UG_BM;
+        const int32_t n0 = n_blk * BN + (int32_t)rank * Cfg::kBNH;
+        const int kb0 = split * kb_per;
+        const int kb1 = (kb0 + kb_per < num_kb_total) ? kb0 + kb_per : num_kb_total;
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1u);
+          uint8_t* sa = stage_base + stage * Cfg::kStageBytes;
+          uint8_t* sb = sa + Cfg::kStageBytesA;
+          if (leader) mbar_arrive_expect_tx(&full_bar[stage], 2u * (uint32_t)Cfg::kStageBytes);
+          if constexpr (A_MN) {
+#pragma unroll
+            for (int a = 0; a < UG_BM / 64; ++a) tma_load_2d_2sm(sa + a * kAtomBytes, &tmA, &full_bar[stage], m0 + 64 * a, kb * UG_BK);
+          } else {
+            tma_load_2d_2sm(sa, &tmA, &full_bar[stage], kb * UG_BK, m0);
+          }
+          if constexpr (B_MN) {
+#pragma unroll
+            for (int a = 0; a < Cfg::kBNH / 64; ++a) tma_load_2d_2sm(sb + a * kAtomBytes, &tmB, &full_bar[stage], n0 + 64 * a, kb * UG_BK);
+          } else {
+            tma_load_2d_2sm(sb, &tmB, &full_bar[stage], kb * UG_BK, n0);
+          }
+          if (++stage == kStages) { stage = 0; phase ^= 1u; }
+        }
+      }
+    }
+  } else if (warp == 1 && leader) {
+    // ===================== MMA issuer (leader CTA) =====================
+    constexpr uint32_t idesc = umma_idesc_bf16(BM2, BN, A_MN, B_MN);
+    int stage = 0;
+    uint32_t phase = 0;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int64_t item = cluster_id; item < num_items; item += num_clusters) {
+      const int split = (int)(item % splits);
+      const int kb0 = split * kb_per;
+      const int kb1 = (kb0 + kb_per < num_kb_total) ? kb0 + kb_per : num_kb_total;
+      mbar_wait(&tempty_bar[acc], acc_phase ^ 1u);
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
+      for (int kb = kb0; kb < kb1; ++kb) {
+        mbar_wait(&full_bar[stage], phase);
+        tc_fence_after();
+        if (elect_one()) {
+          const uint32_t sa = smem_u32(stage_base + stage * Cfg::kStageBytes);
+          const uint32_t sb = sa + Cfg::kStageBytesA;
+          const uint64_t da = A_MN ? umma_desc_mn_sw128(sa, kAtomBytes) : umma_desc_k_sw128(sa);
+          const uint64_t db = B_MN ? umma_desc_mn_sw128(sb, kAtomBytes) : umma_desc_k_sw128(sb);
+          constexpr uint64_t ka = A_MN ? 128 : 2;
+          constexpr uint64_t kbs = B_MN ? 128 : 2;
+#pragma unroll
+          for (int k = 0; k < UG_BK / 16; ++k)
+            umma_bf16_2sm(d_tmem, da + ka * (uint64_t)k, db + kbs * (uint64_t)k, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+          umma_commit_2sm(&empty_bar[stage]);
+          if (kb == kb1 - 1) umma_commit_2sm(&tfull_bar[acc]);
+        }
+        __syncwarp();
+        if (++stage == kStages) { stage = 0; phase ^= 1u; }
+      }
+      if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
+    }
+  } else if (warp >= 4) {
+    // ===================== epilogue (this CTA's 128 rows) =====================
+    const int q = warp & 3;          // TMEM lane quarter
+    const int cg = (warp - 4) >> 2;  // column half of the tile
+    constexpr int kColsPerGroup = BN / 2;
+    uint8_t* wsm = smem + kStages * Cfg::kStageBytes + Cfg::kBarBytes + (warp - 4) * PE_WARP_BYTES;
+    const WarpStage ws{reinterpret_cast<float*>(wsm), reinterpret_cast<uint32_t*>(wsm + 32 * PE_F32_LD * 4)};
+    constexpr bool kStaged = (KIND == EPI_LNMOD || KIND == EPI_GATED_RES || KIND == EPI_SILU_ACT || KIND == EPI_STORE_ACT);
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int64_t item = cluster_id; item < num_items; item += num_clusters) {
+      int64_t m_blk; int n_blk;
+      ug_tile_coords(item / splits, m_tiles, n_tiles, gm, m_blk, n_blk);
+      const int64_t row0 = m_blk * BM2 + (int64_t)rank * UG_BM + q * 32;  // first row of this warp
+      const int64_t left = M - row0;
+      const int rows_valid = left >= 32 ? 32 : (left > 0 ? (int)left : 0);
+      const int64_t row = row0 + lane;
+      const bool row_ok = lane < rows_valid;
+      const int n0 = n_blk * BN + cg * kColsPerGroup;
+      const uint32_t t_tile = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN);
+      if constexpr (KIND == EPI_LNMOD) {
+        const int W = ep.ln_width;
+        if (n_blk < ep.ln_tiles) {
+          // (shift | scale) tile: this warp owns feature columns f0 .. f0+63 of its 32 rows
+          const int f0 = n_blk * 128 + cg * 64;
+          float4 hreg[8];
+          tile_ldg_f32(ep.res + row0 * ep.ldo + f0, ep.ldo, rows_valid, lane, hreg);
+          float mean = 0.f, rstd = 0.f;
+          if (row_ok) {  // row sums written by the producer of h, one (sum, sum of squares) per 128 columns
+            const float4* sp = reinterpret_cast<const float4*>(ep.stats + row * (W / 64));
+            float s = 0.f, ss = 0.f;
+            for (int i = 0; i < W / 256; ++i) {
+              const float4 t = sp[i];
+              s += t.x + t.z;
+              ss += t.y + t.w;
+            }
+            mean = s / (float)W;
+            rstd = rsqrtf(fmaxf(ss / (float)W - mean * mean, 0.f) + 1e-6f);
+          }
+          mbar_wait(&tfull_bar[acc], acc_phase);
+          tc_fence_after();
+#pragma unroll 1
+          for (int c0 = 0; c0 < 64; c0 += 32) {
+            uint32_t sh[32], sc[32];
+            tmem_ld_32x32(t_tile + (uint32_t)(cg * 64 + c0), sh);
+            tmem_ld_32x32(t_tile + (uint32_t)(128 + cg * 64 + c0), sc);
+            float hrow[32];
+            tile_to_row_f32(ws.f, lane, hreg, hrow);
+            if (c0 == 0) tile_ldg_f32(ep.res + row0 * ep.ldo + f0 + 32, ep.ldo, rows_valid, lane, hreg);
+            tmem_ld_wait();
+            const float* bsh = ep.bias + n_blk * 256 + cg * 64 + c0;
+            uint32_t pk[16];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              const float4 b1 = __ldg(reinterpret_cast<const float4*>(bsh) + i);
+              const float4 b2 = __ldg(reinterpret_cast<const float4*>(bsh + 128) + i);
+              float n0_ = (hrow[4 * i] - mean) * rstd, n1_ = (hrow[4 * i + 1] - mean) * rstd;
+              float n2_ = (hrow[4 * i + 2] - mean) * rstd, n3_ = (hrow[4 * i + 3] - mean) * rstd;
+              if (ep.ln_w != nullptr) {
+                const float4 g = __ldg(reinterpret_cast<const float4*>(ep.ln_w + f0 + c0) + i);
+                const float4 bb = __ldg(reinterpret_cast<const float4*>(ep.ln_b + f0 + c0) + i);
+                n0_ = fmaf(n0_, g.x, bb.x); n1_ = fmaf(n1_, g.y, bb.y); n2_ = fmaf(n2_, g.z, bb.z); n3_ = fmaf(n3_, g.w, bb.w);
+              }
+              const float o0 = fmaf(n0_, 1.0f + (__uint_as_float(sc[4 * i]) + b2.x), __uint_as_float(sh[4 * i]) + b1.x);
+              const float o1 = fmaf(n1_, 1.0f + (__uint_as_float(sc[4 * i + 1]) + b2.y), __uint_as_float(sh[4 * i + 1]) + b1.y);
+              const float o2 = fmaf(n2_, 1.0f + (__uint_as_float(sc[4 * i + 2]) + b2.z), __uint_as_float(sh[4 * i + 2]) + b1.z);
+              const float o3 = fmaf(n3_, 1.0f + (__uint_as_float(sc[4 * i + 3]) + b2.w), __uint_as_float(sh[4 * i + 3]) + b1.w);
+              pk[2 * i] = pack_bf16x2(o0, o1);
+              pk[2 * i + 1] = pack_bf16x2(o2, o3);
+            }
+            row_stg_b16(ws.b, reinterpret_cast<bf16*>(ep.out) + row0 * ep.ldo + f0 + c0, ep.ldo, rows_valid, lane, pk);
+          }
+        } else {
+          // gate tile: bf16 store into out2
+          const int g0 = (n_blk - ep.ln_tiles) * BN + cg * 128;
+          mbar_wait(&tfull_bar[acc], acc_phase);
+          tc_fence_after();
+#pragma unroll 1
+          for (int c0 = 0; c0 < 128; c0 += 32) {
+            uint32_t v[32];
+            tmem_ld_32x32(t_tile + (uint32_t)(cg * 128 + c0), v);
+            float b[32];
+            bias32_ldg(ep.bias + n_blk * 256 + cg * 128 + c0, b);
+            tmem_ld_wait();
+            uint32_t pk[16];
+#pragma unroll
+            for (int i = 0; i < 16; ++i) pk[i] = pack_bf16x2(__uint_as_float(v[2 * i]) + b[2 * i], __uint_as_float(v[2 * i + 1]) + b[2 * i + 1]);
+            row_stg_b16(ws.b, reinterpret_cast<bf16*>(ep.out2) + row0 * ep.ldo2 + g0 + c0, ep.ldo2, rows_valid, lane, pk);
+          }
+        }
+      } else if constexpr (KIND == EPI_GATED_RES) {
+        // h[rows, n0..] = h + gate * (acc + bias), fp32 residual stream in place; row sums for the next LayerNorm
+        const float* resp = (ep.res != nullptr ? ep.res : reinterpret_cast<const float*>(ep.out)) + row0 * ep.ldo + n0;
+        float* outp = reinterpret_cast<float*>(ep.out) + row0 * ep.ldo + n0;
+        const bf16* gatep = reinterpret_cast<const bf16*>(ep.aux) + row0 * ep.ldaux + n0;
+        float4 hreg[8];
+        uint4 greg[4];
+        tile_ldg_f32(resp, ep.ldo, rows_valid, lane, hreg);
+        tile_ldg_b16(gatep, ep.ldaux, rows_valid, lane, greg);
+        float s = 0.f, ss = 0.f;
+        mbar_wait(&tfull_bar[acc], acc_phase);
+        tc_fence_after();
+#pragma unroll 1
+        for (int c0 = 0; c0 < kColsPerGroup; c0 += 32) {
+          uint32_t v[32];
+          tmem_ld_32x32(t_tile + (uint32_t)(cg * kColsPerGroup + c0), v);
+          float hrow[32];
+          uint32_t grow[16];
+          tile_to_row_f32(ws.f, lane, hreg, hrow);
+          tile_to_row_b16(ws.b, lane, greg, grow);
+          if (c0 + 32 < kColsPerGroup) {
+            tile_ldg_f32(resp + c0 + 32, ep.ldo, rows_valid, lane, hreg);
+            tile_ldg_b16(gatep + c0 + 32, ep.ldaux, rows_valid, lane, greg);
+          }
+          float b[32];
+          bias32_ldg(ep.bias != nullptr ? ep.bias + n0 + c0 : nullptr, b);
+          tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            const float2 g2 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&grow[i]));
+            hrow[2 * i] = fmaf(g2.x, __uint_as_float(v[2 * i]) + b[2 * i], hrow[2 * i]);
+            hrow[2 * i + 1] = fmaf(g2.y, __uint_as_float(v[2 * i + 1]) + b[2 * i + 1], hrow[2 * i + 1]);
+            s += hrow[2 * i] + hrow[2 * i + 1];
+            ss += hrow[2 * i] * hrow[2 * i] + hrow[2 * i + 1] * hrow[2 * i + 1];
+          }
+          row_stg_f32(ws.f, outp + c0, ep.ldo, rows_valid, lane, hrow);
+        }
+        if (ep.stats != nullptr && row_ok)
+          *reinterpret_cast<float2*>(ep.stats + (row * (ep.ln_width / 128) + n_blk * 2 + cg) * 2) = make_float2(s, ss);
+      } else if constexpr (KIND == EPI_SILU_ACT || KIND == EPI_STORE_ACT) {
+        bf16* outp = reinterpret_cast<bf16*>(ep.out) + row0 * ep.ldo + n0;
+        mbar_wait(&tfull_bar[acc], acc_phase);
+        tc_fence_after();
+#pragma unroll 1
+        for (int c0 = 0; c0 < kColsPerGroup; c0 += 32) {
+          uint32_t v[32];
+          tmem_ld_32x32(t_tile + (uint32_t)(cg * kColsPerGroup + c0), v);
+          float b[32];
+          bias32_ldg(ep.bias != nullptr ? ep.bias + n0 + c0 : nullptr, b);
+          tmem_ld_wait();
+          uint32_t pk[16];
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            float x0 = __uint_as_float(v[2 * i]) + b[2 * i], x1 = __uint_as_float(v[2 * i + 1]) + b[2 * i + 1];
+            if constexpr (KIND == EPI_SILU_ACT) {
+              x0 = __fdividef(x0, 1.0f + __expf(-x0));
+              x1 = __fdividef(x1, 1.0f + __expf(-x1));
+            }
+            pk[i] = pack_bf16x2(x0, x1);
+          }
+          row_stg_b16(ws.b, outp + c0, ep.ldo, rows_valid, lane, pk);
+        }
+      } else {
+        typename RowEpi<KIND, TA>::Pre pre;
+        if (RowEpi<KIND, TA>::kNeedsPrefetch && row_ok) RowEpi<KIND, TA>::prefetch(ep, row, n0, pre);
+        mbar_wait(&tfull_bar[acc], acc_phase);
+        tc_fence_after();
+#pragma unroll 1
+        for (int c0 = 0; c0 < kColsPerGroup; c0 += 32) {
+          uint32_t v[32];
+          tmem_ld_32x32(t_tile + (uint32_t)(cg * kColsPerGroup + c0), v);
+          tmem_ld_wait();
+          if (row_ok) RowEpi<KIND, TA>::store(ep, row, n0 + c0, v, pre);
+          if (RowEpi<KIND, TA>::kNeedsPrefetch && row_ok && c0 + 32 < kColsPerGroup)
+            RowEpi<KIND, TA>::prefetch(ep, row, n0 + c0 + 32, pre);
+        }
+        if (row_ok) RowEpi<KIND, TA>::finish(ep, row, pre);
+      }
+      (void)kStaged;
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(&tempty_bar[acc], 0);
+      if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
+    }
+  }
+
+  tc_fence_before();
+  cluster_sync_all();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc_2sm<Cfg::kTmemCols>(tmem_base);
+  }
+}
+
+}  // namespace uva

@@ -19,6 +19,7 @@
 #include "train_bwd_kernels.cuh"
 #include "train_kernels.cuh"
 #include "umma_gemm.cuh"
+#include "umma_gemm2.cuh"
 
 using namespace uva;
 
@@ -135,7 +136,7 @@ struct DevTables {  // fp32 device copies of one process' tables, [T] each
 struct UvaHead {
   UvaHeadDesc d;
   int num_sms = 148;
-  int64_t chunk_rows = 32768;
+  int64_t chunk_rows = 65536;
   int nmod = 0;  // (3*depth + 2) * W : width of the concatenated AdaLN modulation output
   ScheduleTables gen, train;
   DevTables dtrain;
@@ -153,6 +154,8 @@ struct UvaHead {
   bf16* wb = nullptr;
   size_t wb_elems = 0;
   size_t ob_condw, ob_adaw, ob_linw;      // [W,Z], [nmod,W], [32,W] (zero padded)
+  size_t ob_adaw_p = 0;                   // [nmod,W] in (shift|scale)-tile order (k_pack_ada_perm)
+  float* adab_p = nullptr;                // [nmod] bias in the same order
   std::vector<size_t> ob_w1, ob_w2;       // [W,W]
   bool weights_loaded = false;
   int64_t launches = 0;
@@ -163,6 +166,10 @@ struct UvaHead {
   cudaStream_t side = nullptr;
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   bool overlap = true;
+  bool pair = true;  // CTA-pair (cta_group::2) GEMM for M > 128
+  bool fuse_ln = true;  // UVA_FUSE_LN: LayerNorm-modulate inside the AdaLN GEMM epilogue (bf16 sampling path)
+  int grid_mult = 1;  // UVA_GRID_MULT: GEMM grids of grid_mult x #SMs CTAs (block scheduler balances the tail)
+  int dbg_skip = 0;  // UVA_DEBUG_SKIP (timing diagnosis only, results are wrong): 1 = no GEMM launches, 2 = no row kernels
   bool timing = false;
   int cur_cat = 0;
   struct TimedLaunch { int cat; cudaEvent_t a, b; };
@@ -261,6 +268,10 @@ extern "C" int uva_head_create(const UvaHeadDesc* desc, UvaHead** out) {
     if (v >= 256) h->chunk_rows = (v / 256) * 256;
   }
   if (const char* e = getenv("UVA_OVERLAP")) h->overlap = atoi(e) != 0;
+  if (const char* e = getenv("UVA_PAIR")) h->pair = atoi(e) != 0;
+  if (const char* e = getenv("UVA_FUSE_LN")) h->fuse_ln = atoi(e) != 0;
+  if (const char* e = getenv("UVA_DEBUG_SKIP")) h->dbg_skip = atoi(e);
+  if (const char* e = getenv("UVA_GRID_MULT")) { int v = atoi(e); if (v >= 1 && v <= 64) h->grid_mult = v; }
   CUDA_TRY(cudaStreamCreateWithFlags(&h->side, cudaStreamNonBlocking));
   CUDA_TRY(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
   CUDA_TRY(cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming));
@@ -311,6 +322,8 @@ extern "C" int uva_head_create(const UvaHeadDesc* desc, UvaHead** out) {
     size_t o = 0;
     auto take = [&](size_t n) { size_t r = o; o += (n + 511) / 512 * 512; return r; };
     h->ob_condw = take(W * Z); h->ob_adaw = take((size_t)h->nmod * W); h->ob_linw = take(32 * W);
+    h->ob_adaw_p = take((size_t)h->nmod * W);
+    CUDA_TRY(cudaMalloc(&h->adab_p, (size_t)h->nmod * sizeof(float)));
     for (int b = 0; b < d.depth; ++b) {
       h->ob_w1.push_back(take(W * W)); h->ob_w2.push_back(take(W * W));
     }
@@ -330,7 +343,7 @@ extern "C" int uva_head_create(const UvaHeadDesc* desc, UvaHead** out) {
 extern "C" void uva_head_destroy(UvaHead* h) {
   if (!h) return;
   cudaFree(h->d_tables); cudaFree(h->feat); cudaFree(h->temb); cudaFree(h->temb_hidden); cudaFree(h->temb_pre);
-  cudaFree(h->wf); cudaFree(h->wb);
+  cudaFree(h->wf); cudaFree(h->wb); cudaFree(h->adab_p);
   if (h->side) cudaStreamDestroy(h->side);
   if (h->ev_fork) cudaEventDestroy(h->ev_fork);
   if (h->ev_join) cudaEventDestroy(h->ev_join);
