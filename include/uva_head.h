@@ -146,7 +146,8 @@ int uva_head_timing_read(UvaHead* h, int32_t category, double* total_ms, int64_t
  *   layout 1: A[M,K], B[K,N] (data-gradient form, B MN-major; block_n 256);
  *   layout 2: A[K,M], B[K,N] (weight-gradient form, both MN-major, split-K with vector reductions
  *             ADDED into D, which the caller zero-fills; block_n 256, bias ignored);
- *   layout 8, 9, 10: forms 0, 1, 2 on the CTA-pair (cta_group::2) kernel, 256 x 256 tiles.
+ *   layout 8, 9, 10: forms 0, 1, 2 on the CTA-pair (cta_group::2) kernel, 256 x 256 tiles;
+ *   layout 16, 17, 18: the same on clusters of two pairs with multicast A boxes (N multiple of 512).
  * N multiple of block_n. */
 int uva_gemm_bf16_selftest(const void* A, const void* B, const float* bias, float* D, int64_t M,
                            int32_t N, int32_t K, int32_t block_n, int32_t layout, void* stream);

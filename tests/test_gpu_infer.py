@@ -142,9 +142,14 @@ def test_umma_gemm_wgrad_layout(M, N, K):
     (8, 256, 256, 64), (8, 300, 512, 1024), (8, 4101, 1024, 1024), (8, 129, 256, 128), (8, 20000, 3072, 256),
     (9, 300, 768, 1024), (9, 4101, 1024, 3072), (9, 512, 256, 200),
     (10, 256, 256, 64), (10, 1024, 1024, 16384), (10, 3072, 768, 5000), (10, 200, 256, 130),
+    # clusters of two pairs, A boxes multicast (N multiple of 512)
+    (16, 256, 512, 64), (16, 300, 512, 1024), (16, 4101, 1024, 1024), (16, 129, 512, 128), (16, 20000, 3072, 256),
+    (17, 300, 1024, 1024), (17, 4101, 1024, 3072), (17, 512, 512, 200),
+    (18, 256, 512, 64), (18, 1024, 1024, 16384), (18, 3072, 1024, 5000), (18, 200, 512, 130),
 ])
 def test_umma_pair_gemm_layouts(layout, M, N, K):
-    """CTA-pair (cta_group::2) kernel, 256 x 256 tiles: forward, data-gradient and weight-gradient forms."""
+    """CTA-pair (cta_group::2) kernel, 256 x 256 tiles: forward, data-gradient and weight-gradient forms
+    (layout 8-10: one pair per cluster; 16-18: two pairs per cluster sharing A through TMA multicast)."""
     dev = _cuda()
     from unified_video_action_b200 import _lib
 

@@ -20,61 +20,99 @@
 
 namespace uva {
 
-template <int BN>
+// TMA-fed epilogue (EPI_GATED_RES): the residual tile h (fp32) and the gate tile (bf16) are prefetched by
+// warp 3 into a ring of [128 rows x 32 columns] boxes while the tile's MMAs run; the epilogue warps
+// update the h box in place and one thread per warp group writes it back with a TMA store.
+struct EpiMaps {
+  CUtensorMap h_in;   // fp32 [M, N], box 32 x 128, 128-byte swizzle (residual input)
+  CUtensorMap h_out;  // fp32 [M, N], same box (output; the same tensor when updating in place)
+  CUtensorMap g;      // bf16 [M, N], box 32 x 128, 64-byte swizzle (gate)
+};
+
+template <int BN, int KIND = 0>
 struct Umma2Cfg {
   static constexpr int kBNH = BN / 2;  // B rows per CTA
   static constexpr int kStageBytesA = UG_BM * UG_BK * 2;
   static constexpr int kStageBytesB = kBNH * UG_BK * 2;
   static constexpr int kStageBytes = kStageBytesA + kStageBytesB;
-  static constexpr int kStages = 5;
+  static constexpr bool kTmaEpi = (KIND == EPI_GATED_RES);
+  static constexpr int kStages = kTmaEpi ? 4 : 5;
+  static constexpr int kRing = 4;                         // epilogue prefetch ring (kTmaEpi)
+  static constexpr int kSlotH = UG_BM * 32 * 4;           // 16 KB
+  static constexpr int kSlotG = UG_BM * 32 * 2;           //  8 KB
+  static constexpr int kSlotBytes = kSlotH + kSlotG;
+  static constexpr int kEpiBytes = kTmaEpi ? kRing * kSlotBytes : 8 * PE_WARP_BYTES;
   static constexpr int kBarBytes = 256;
-  static constexpr int kSmemBytes = 1024 + kStages * kStageBytes + kBarBytes + 8 * PE_WARP_BYTES;  // + epilogue staging
+  static constexpr int kSmemBytes = 1024 + kStages * kStageBytes + kEpiBytes + kBarBytes;
   static constexpr uint32_t kTmemCols = 512;  // 2 accumulator stages x 256 columns
 };
 
-template <int BN, int KIND, typename TA, bool A_MN = false, bool B_MN = false>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(UG_THREADS, 1)
+// CL = 2: one pair per cluster.  CL = 4: two pairs per cluster work on the SAME 256 rows and on two
+// adjacent 256-column tiles; every A box is loaded once and multicast to both pairs (each CTA fetches
+// 64 of the 128 rows its half needs), so a CTA pulls 24 KB instead of 32 KB per k-block through the
+// L2 -> SMEM path, which is what bounds the CL = 2 kernel (profiles/r01_ncu_full_gemm2_v3_summary.txt).
+// The cluster size is a launch attribute (cudaLaunchAttributeClusterDimension).
+template <int BN, int KIND, typename TA, bool A_MN = false, bool B_MN = false, int CL = 2>
+__global__ void __launch_bounds__(UG_THREADS, 1)
 umma_gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                  int64_t M, int N, int K, int gm, int splits, EpiArgs ep) {
+                  const __grid_constant__ EpiMaps em, int64_t M, int N, int K, int gm, int splits, EpiArgs ep) {
   static_assert(BN == 256, "CTA-pair kernel: 256 x 256 tiles");
-  using Cfg = Umma2Cfg<BN>;
+  using Cfg = Umma2Cfg<BN, KIND>;
   constexpr int kStages = Cfg::kStages;
   constexpr int BM2 = 2 * UG_BM;
   constexpr uint32_t kAtomBytes = 64 * UG_BK * 2;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* stage_base = smem;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kStages * Cfg::kStageBytes);
+  uint8_t* epi_smem = smem + kStages * Cfg::kStageBytes;  // per-warp staging tiles or the TMA ring (1024-aligned)
+  uint64_t* bars = reinterpret_cast<uint64_t*>(epi_smem + Cfg::kEpiBytes);
   uint64_t* full_bar = bars;                      // [kStages] (used in the leader CTA)
   uint64_t* empty_bar = bars + kStages;           // [kStages] (each CTA its own, multicast commit)
   uint64_t* tfull_bar = bars + 2 * kStages;       // [2]       (each CTA its own, multicast commit)
   uint64_t* tempty_bar = bars + 2 * kStages + 2;  // [2]       (used in the leader CTA)
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 4);
+  uint64_t* efull_bar = bars + 2 * kStages + 4;                  // [kRing] epilogue prefetch ring (this CTA)
+  uint64_t* eempty_bar = bars + 2 * kStages + 4 + Cfg::kRing;    // [kRing]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 4 + 2 * Cfg::kRing);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const uint32_t rank = cluster_ctarank();
+  static_assert(CL == 2 || CL == 4, "cluster of one or two CTA pairs");
+  const uint32_t crank = cluster_ctarank();
+  const uint32_t rank = crank & 1u;   // position inside the pair
+  const uint32_t pair = crank >> 1;   // pair inside the cluster (0 when CL == 2)
   const bool leader = rank == 0;
-  const int64_t cluster_id = blockIdx.x >> 1;
-  const int64_t num_clusters = gridDim.x >> 1;
+  const int64_t cluster_id = blockIdx.x / CL;
+  const int64_t num_clusters = gridDim.x / CL;
   const int64_t m_tiles = (M + BM2 - 1) / BM2;
-  const int n_tiles = N / BN;
+  constexpr int kPairs = CL / 2;
+  const int n_tiles = N / BN / kPairs;  // column tiles (CL == 2) or pairs of adjacent column tiles (CL == 4)
   const int64_t num_items = m_tiles * n_tiles * splits;
+  const uint16_t pair_mask = (uint16_t)(3u << (2 * pair));
+  constexpr uint16_t kAllMask = (uint16_t)((1u << CL) - 1u);
   const int num_kb_total = (K + UG_BK - 1) / UG_BK;
   const int kb_per = (num_kb_total + splits - 1) / splits;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
+    if constexpr (Cfg::kTmaEpi) {
+      tma_prefetch_desc(&em.h_in);
+      tma_prefetch_desc(&em.h_out);
+      tma_prefetch_desc(&em.g);
+    }
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < kStages; ++s) {
       mbar_init(&full_bar[s], 1);
-      mbar_init(&empty_bar[s], 1);
+      mbar_init(&empty_bar[s], kPairs);  // every pair that receives this CTA's boxes releases the slot
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&tfull_bar[s], 1);
       mbar_init(&tempty_bar[s], 16);
+    }
+    for (int s = 0; s < Cfg::kRing; ++s) {
+      mbar_init(&efull_bar[s], 1);
+      mbar_init(&eempty_bar[s], 1);
     }
     fence_mbar_init();
   }
@@ -95,7 +133,7 @@ umma_gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         const int split = (int)(item - tile * splits);
         ug_tile_coords(tile, m_tiles, n_tiles, gm, m_blk, n_blk);
         const int32_t m0 = (int32_t)(m_blk * BM2) + (int32_t)rank * UG_BM;
-        const int32_t n0 = n_blk * BN + (int32_t)rank * Cfg::kBNH;
+        const int32_t n0 = (n_blk * kPairs + (int32_t)pair) * BN + (int32_t)rank * Cfg::kBNH;
         const int kb0 = split * kb_per;
         const int kb1 = (kb0 + kb_per < num_kb_total) ? kb0 + kb_per : num_kb_total;
         for (int kb = kb0; kb < kb1; ++kb) {
@@ -103,7 +141,12 @@ umma_gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           uint8_t* sa = stage_base + stage * Cfg::kStageBytes;
           uint8_t* sb = sa + Cfg::kStageBytesA;
           if (leader) mbar_arrive_expect_tx(&full_bar[stage], 2u * (uint32_t)Cfg::kStageBytes);
-          if constexpr (A_MN) {
+          if constexpr (CL == 4) {
+            // this CTA fetches rows [64 pair, +64) of its half's 128 A rows for both pairs (box: 64 x 64)
+            const uint16_t mc = (uint16_t)(5u << rank);
+            if constexpr (A_MN) tma_load_2d_2sm_mc(sa + pair * kAtomBytes, &tmA, &full_bar[stage], m0 + 64 * (int32_t)pair, kb * UG_BK, mc);
+            else tma_load_2d_2sm_mc(sa + pair * kAtomBytes, &tmA, &full_bar[stage], kb * UG_BK, m0 + 64 * (int32_t)pair, mc);
+          } else if constexpr (A_MN) {
 #pragma unroll
             for (int a = 0; a < UG_BM / 64; ++a) tma_load_2d_2sm(sa + a * kAtomBytes, &tmA, &full_bar[stage], m0 + 64 * a, kb * UG_BK);
           } else {
@@ -146,27 +189,52 @@ umma_gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 #pragma unroll
           for (int k = 0; k < UG_BK / 16; ++k)
             umma_bf16_2sm(d_tmem, da + ka * (uint64_t)k, db + kbs * (uint64_t)k, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
-          umma_commit_2sm(&empty_bar[stage]);
-          if (kb == kb1 - 1) umma_commit_2sm(&tfull_bar[acc]);
+          umma_commit_2sm(&empty_bar[stage], kAllMask);
+          if (kb == kb1 - 1) umma_commit_2sm(&tfull_bar[acc], pair_mask);
         }
         __syncwarp();
         if (++stage == kStages) { stage = 0; phase ^= 1u; }
       }
       if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
     }
+  } else if (warp == 3) {
+    // ===================== epilogue operand prefetch (TMA-fed epilogue kinds) =====================
+    if constexpr (Cfg::kTmaEpi) {
+      if (elect_one()) {
+        uint32_t seq = 0;
+        for (int64_t item = cluster_id; item < num_items; item += num_clusters) {
+          int64_t m_blk; int n_blk;
+          ug_tile_coords(item / splits, m_tiles, n_tiles, gm, m_blk, n_blk);
+          n_blk = n_blk * kPairs + (int)pair;
+          const int32_t r0 = (int32_t)(m_blk * BM2) + (int32_t)rank * UG_BM;
+          const int32_t c0 = n_blk * BN;
+          for (int blk = 0; blk < BN / 32; ++blk, ++seq) {
+            const int slot = (int)(seq % Cfg::kRing);
+            const uint32_t ph = (seq / Cfg::kRing) & 1u;
+            mbar_wait(&eempty_bar[slot], ph ^ 1u);
+            uint8_t* sp = epi_smem + slot * Cfg::kSlotBytes;
+            mbar_arrive_expect_tx(&efull_bar[slot], (uint32_t)Cfg::kSlotBytes);
+            tma_load_2d(sp, &em.h_in, &efull_bar[slot], c0 + 32 * blk, r0);
+            tma_load_2d(sp + Cfg::kSlotH, &em.g, &efull_bar[slot], c0 + 32 * blk, r0);
+          }
+        }
+      }
+    }
   } else if (warp >= 4) {
     // ===================== epilogue (this CTA's 128 rows) =====================
     const int q = warp & 3;          // TMEM lane quarter
     const int cg = (warp - 4) >> 2;  // column half of the tile
     constexpr int kColsPerGroup = BN / 2;
-    uint8_t* wsm = smem + kStages * Cfg::kStageBytes + Cfg::kBarBytes + (warp - 4) * PE_WARP_BYTES;
+    uint8_t* wsm = epi_smem + (Cfg::kTmaEpi ? 0 : (warp - 4) * PE_WARP_BYTES);
     const WarpStage ws{reinterpret_cast<float*>(wsm), reinterpret_cast<uint32_t*>(wsm + 32 * PE_F32_LD * 4)};
     constexpr bool kStaged = (KIND == EPI_LNMOD || KIND == EPI_GATED_RES || KIND == EPI_SILU_ACT || KIND == EPI_STORE_ACT);
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int64_t item = cluster_id; item < num_items; item += num_clusters) {
+    uint32_t tile_seq = 0;  // tiles this CTA has finished (ring position of the TMA-fed epilogue)
+    for (int64_t item = cluster_id; item < num_items; item += num_clusters, ++tile_seq) {
       int64_t m_blk; int n_blk;
       ug_tile_coords(item / splits, m_tiles, n_tiles, gm, m_blk, n_blk);
+      n_blk = n_blk * kPairs + (int)pair;
       const int64_t row0 = m_blk * BM2 + (int64_t)rank * UG_BM + q * 32;  // first row of this warp
       const int64_t left = M - row0;
       const int rows_valid = left >= 32 ? 32 : (left > 0 ? (int)left : 0);
@@ -245,41 +313,58 @@ umma_gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           }
         }
       } else if constexpr (KIND == EPI_GATED_RES) {
-        // h[rows, n0..] = h + gate * (acc + bias), fp32 residual stream in place; row sums for the next LayerNorm
-        const float* resp = (ep.res != nullptr ? ep.res : reinterpret_cast<const float*>(ep.out)) + row0 * ep.ldo + n0;
-        float* outp = reinterpret_cast<float*>(ep.out) + row0 * ep.ldo + n0;
-        const bf16* gatep = reinterpret_cast<const bf16*>(ep.aux) + row0 * ep.ldaux + n0;
-        float4 hreg[8];
-        uint4 greg[4];
-        tile_ldg_f32(resp, ep.ldo, rows_valid, lane, hreg);
-        tile_ldg_b16(gatep, ep.ldaux, rows_valid, lane, greg);
+        // h[rows, cols] = h + gate * (acc + bias) on the fp32 residual stream + row sums for the next LayerNorm.
+        // Warp group cg takes the 32-column boxes blk = cg, cg + 2, ... of the prefetch ring.
+        const int r = q * 32 + lane;  // row inside this CTA's 128-row box
+        const int32_t r0cta = (int32_t)(m_blk * BM2) + (int32_t)rank * UG_BM;
         float s = 0.f, ss = 0.f;
         mbar_wait(&tfull_bar[acc], acc_phase);
         tc_fence_after();
 #pragma unroll 1
-        for (int c0 = 0; c0 < kColsPerGroup; c0 += 32) {
+        for (int bi = 0; bi < BN / 64; ++bi) {
+          const int blk = 2 * bi + cg;
+          const uint32_t seq = tile_seq * (BN / 32) + (uint32_t)blk;
+          const int slot = (int)(seq % Cfg::kRing);
+          const uint32_t ph = (seq / Cfg::kRing) & 1u;
+          uint8_t* sp = epi_smem + slot * Cfg::kSlotBytes;
           uint32_t v[32];
-          tmem_ld_32x32(t_tile + (uint32_t)(cg * kColsPerGroup + c0), v);
-          float hrow[32];
-          uint32_t grow[16];
-          tile_to_row_f32(ws.f, lane, hreg, hrow);
-          tile_to_row_b16(ws.b, lane, greg, grow);
-          if (c0 + 32 < kColsPerGroup) {
-            tile_ldg_f32(resp + c0 + 32, ep.ldo, rows_valid, lane, hreg);
-            tile_ldg_b16(gatep + c0 + 32, ep.ldaux, rows_valid, lane, greg);
-          }
+          tmem_ld_32x32(t_tile + (uint32_t)(blk * 32), v);
           float b[32];
-          bias32_ldg(ep.bias != nullptr ? ep.bias + n0 + c0 : nullptr, b);
+          bias32_ldg(ep.bias != nullptr ? ep.bias + n_blk * BN + blk * 32 : nullptr, b);
+          mbar_wait(&efull_bar[slot], ph);
+          float4 hv[8];
+          uint4 gv[4];
+          uint8_t* hrow = sp + r * 128;
+          const uint8_t* grow = sp + Cfg::kSlotH + r * 64;
+#pragma unroll
+          for (int i = 0; i < 8; ++i) hv[i] = *reinterpret_cast<const float4*>(hrow + ((i ^ (r & 7)) << 4));
+#pragma unroll
+          for (int i = 0; i < 4; ++i) gv[i] = *reinterpret_cast<const uint4*>(grow + ((i ^ ((r >> 1) & 3)) << 4));
           tmem_ld_wait();
 #pragma unroll
-          for (int i = 0; i < 16; ++i) {
-            const float2 g2 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&grow[i]));
-            hrow[2 * i] = fmaf(g2.x, __uint_as_float(v[2 * i]) + b[2 * i], hrow[2 * i]);
-            hrow[2 * i + 1] = fmaf(g2.y, __uint_as_float(v[2 * i + 1]) + b[2 * i + 1], hrow[2 * i + 1]);
-            s += hrow[2 * i] + hrow[2 * i + 1];
-            ss += hrow[2 * i] * hrow[2 * i] + hrow[2 * i + 1] * hrow[2 * i + 1];
+          for (int i = 0; i < 8; ++i) {
+            const uint4 gq = gv[i >> 1];
+            const uint32_t w0 = (i & 1) ? gq.z : gq.x, w1 = (i & 1) ? gq.w : gq.y;
+            const float2 ga = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w0));
+            const float2 gb = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w1));
+            float4 o = hv[i];
+            o.x = fmaf(ga.x, __uint_as_float(v[4 * i]) + b[4 * i], o.x);
+            o.y = fmaf(ga.y, __uint_as_float(v[4 * i + 1]) + b[4 * i + 1], o.y);
+            o.z = fmaf(gb.x, __uint_as_float(v[4 * i + 2]) + b[4 * i + 2], o.z);
+            o.w = fmaf(gb.y, __uint_as_float(v[4 * i + 3]) + b[4 * i + 3], o.w);
+            s += (o.x + o.y) + (o.z + o.w);
+            ss += (o.x * o.x + o.y * o.y) + (o.z * o.z + o.w * o.w);
+            *reinterpret_cast<float4*>(hrow + ((i ^ (r & 7)) << 4)) = o;
           }
-          row_stg_f32(ws.f, outp + c0, ep.ldo, rows_valid, lane, hrow);
+          fence_proxy_async();
+          named_bar_sync(1 + cg, 128);
+          if (q == 0 && lane == 0) {
+            tma_store_2d(&em.h_out, sp, n_blk * BN + blk * 32, r0cta);
+            bulk_commit_group();
+            bulk_wait_read_all();
+            mbar_arrive(&eempty_bar[slot]);
+          }
+          __syncwarp();
         }
         if (ep.stats != nullptr && row_ok)
           *reinterpret_cast<float2*>(ep.stats + (row * (ep.ln_width / 128) + n_blk * 2 + cg) * 2) = make_float2(s, ss);
@@ -325,11 +410,14 @@ umma_gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       (void)kStaged;
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive_cluster(&tempty_bar[acc], 0);
+      if (lane == 0) mbar_arrive_cluster(&tempty_bar[acc], crank & ~1u);
       if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
     }
   }
 
+  if constexpr (Cfg::kTmaEpi) {
+    if (warp >= 4 && (warp & 3) == 0 && lane == 0) bulk_wait_all();  // this thread's TMA stores have landed
+  }
   tc_fence_before();
   cluster_sync_all();
   if (warp == 2) {

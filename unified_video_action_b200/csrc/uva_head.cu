@@ -167,6 +167,7 @@ struct UvaHead {
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   bool overlap = true;
   bool pair = true;  // CTA-pair (cta_group::2) GEMM for M > 128
+  bool quad = false;  // UVA_QUAD: clusters of two CTA pairs with multicast A boxes (forward-form GEMMs)
   bool fuse_ln = true;  // UVA_FUSE_LN: LayerNorm-modulate inside the AdaLN GEMM epilogue (bf16 sampling path)
   int grid_mult = 1;  // UVA_GRID_MULT: GEMM grids of grid_mult x #SMs CTAs (block scheduler balances the tail)
   int dbg_skip = 0;  // UVA_DEBUG_SKIP (timing diagnosis only, results are wrong): 1 = no GEMM launches, 2 = no row kernels
@@ -269,6 +270,7 @@ extern "C" int uva_head_create(const UvaHeadDesc* desc, UvaHead** out) {
   }
   if (const char* e = getenv("UVA_OVERLAP")) h->overlap = atoi(e) != 0;
   if (const char* e = getenv("UVA_PAIR")) h->pair = atoi(e) != 0;
+  if (const char* e = getenv("UVA_QUAD")) h->quad = atoi(e) != 0;
   if (const char* e = getenv("UVA_FUSE_LN")) h->fuse_ln = atoi(e) != 0;
   if (const char* e = getenv("UVA_DEBUG_SKIP")) h->dbg_skip = atoi(e);
   if (const char* e = getenv("UVA_GRID_MULT")) { int v = atoi(e); if (v >= 1 && v <= 64) h->grid_mult = v; }
