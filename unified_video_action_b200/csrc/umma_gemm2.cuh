@@ -23,10 +23,12 @@ namespace uva {
 // TMA-fed epilogue (EPI_GATED_RES): the residual tile h (fp32) and the gate tile (bf16) are prefetched by
 // warp 3 into a ring of [128 rows x 32 columns] boxes while the tile's MMAs run; the epilogue warps
 // update the h box in place and one thread per warp group writes it back with a TMA store.
+// EPI_LNMOD uses the same ring: h boxes are prefetched for the (shift | scale) tiles, and every output
+// box (a, gate: bf16) is staged in the 8 KB part of a slot and written with a TMA store.
 struct EpiMaps {
-  CUtensorMap h_in;   // fp32 [M, N], box 32 x 128, 128-byte swizzle (residual input)
-  CUtensorMap h_out;  // fp32 [M, N], same box (output; the same tensor when updating in place)
-  CUtensorMap g;      // bf16 [M, N], box 32 x 128, 64-byte swizzle (gate)
+  CUtensorMap h_in;   // fp32 [M, W], box 32 x 128, 128-byte swizzle (residual stream input)
+  CUtensorMap h_out;  // GATED_RES: fp32 output, same geometry as h_in.  LNMOD: bf16 gate output [M, W], 64-byte swizzle
+  CUtensorMap g;      // GATED_RES: bf16 gate input [M, N], box 32 x 128, 64-byte swizzle.  LNMOD: bf16 `a` output [M, W]
 };
 
 template <int BN, int KIND = 0>
@@ -35,7 +37,7 @@ struct Umma2Cfg {
   static constexpr int kStageBytesA = UG_BM * UG_BK * 2;
   static constexpr int kStageBytesB = kBNH * UG_BK * 2;
   static constexpr int kStageBytes = kStageBytesA + kStageBytesB;
-  static constexpr bool kTmaEpi = (KIND == EPI_GATED_RES);
+  static constexpr bool kTmaEpi = (KIND == EPI_GATED_RES || KIND == EPI_LNMOD);
   static constexpr int kStages = kTmaEpi ? 4 : 5;
   static constexpr int kRing = 4;                         // epilogue prefetch ring (kTmaEpi)
   static constexpr int kSlotH = UG_BM * 32 * 4;           // 16 KB
@@ -208,14 +210,25 @@ umma_gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           n_blk = n_blk * kPairs + (int)pair;
           const int32_t r0 = (int32_t)(m_blk * BM2) + (int32_t)rank * UG_BM;
           const int32_t c0 = n_blk * BN;
-          for (int blk = 0; blk < BN / 32; ++blk, ++seq) {
+          const bool ln_tile = (KIND == EPI_LNMOD) && n_blk < ep.ln_tiles;
+          const int nblk = ln_tile ? 4 : BN / 32;
+          for (int blk = 0; blk < nblk; ++blk, ++seq) {
             const int slot = (int)(seq % Cfg::kRing);
             const uint32_t ph = (seq / Cfg::kRing) & 1u;
             mbar_wait(&eempty_bar[slot], ph ^ 1u);
             uint8_t* sp = epi_smem + slot * Cfg::kSlotBytes;
-            mbar_arrive_expect_tx(&efull_bar[slot], (uint32_t)Cfg::kSlotBytes);
-            tma_load_2d(sp, &em.h_in, &efull_bar[slot], c0 + 32 * blk, r0);
-            tma_load_2d(sp + Cfg::kSlotH, &em.g, &efull_bar[slot], c0 + 32 * blk, r0);
+            if constexpr (KIND == EPI_LNMOD) {
+              if (ln_tile) {  // residual columns of this tile's 128 features
+                mbar_arrive_expect_tx(&efull_bar[slot], (uint32_t)Cfg::kSlotH);
+                tma_load_2d(sp, &em.h_in, &efull_bar[slot], n_blk * 128 + 32 * blk, r0);
+              } else {
+                mbar_arrive(&efull_bar[slot]);  // gate tile: the slot is only an output staging buffer
+              }
+            } else {
+              mbar_arrive_expect_tx(&efull_bar[slot], (uint32_t)Cfg::kSlotBytes);
+              tma_load_2d(sp, &em.h_in, &efull_bar[slot], c0 + 32 * blk, r0);
+              tma_load_2d(sp + Cfg::kSlotH, &em.g, &efull_bar[slot], c0 + 32 * blk, r0);
+            }
           }
         }
       }
@@ -231,6 +244,7 @@ umma_gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     int acc = 0;
     uint32_t acc_phase = 0;
     uint32_t tile_seq = 0;  // tiles this CTA has finished (ring position of the TMA-fed epilogue)
+    uint32_t seq_base = 0;  // EPI_LNMOD: ring boxes consumed by the finished tiles (4 or 8 per tile)
     for (int64_t item = cluster_id; item < num_items; item += num_clusters, ++tile_seq) {
       int64_t m_blk; int n_blk;
       ug_tile_coords(item / splits, m_tiles, n_tiles, gm, m_blk, n_blk);
@@ -244,17 +258,18 @@ umma_gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       const uint32_t t_tile = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN);
       if constexpr (KIND == EPI_LNMOD) {
         const int W = ep.ln_width;
+        const int r = q * 32 + lane;  // row inside this CTA's 128-row box
+        const int32_t r0cta = (int32_t)(m_blk * BM2) + (int32_t)rank * UG_BM;
+        const uint32_t rsw = (uint32_t)((r >> 1) & 3);
         if (n_blk < ep.ln_tiles) {
-          // (shift | scale) tile: this warp owns feature columns f0 .. f0+63 of its 32 rows
-          const int f0 = n_blk * 128 + cg * 64;
-          float4 hreg[8];
-          tile_ldg_f32(ep.res + row0 * ep.ldo + f0, ep.ldo, rows_valid, lane, hreg);
+          // (shift | scale) tile: warp group cg takes the 32-feature boxes j = cg, cg + 2 of features f0 .. f0+127
+          const int f0 = n_blk * 128;
           float mean = 0.f, rstd = 0.f;
           if (row_ok) {  // row sums written by the producer of h, one (sum, sum of squares) per 128 columns
-            const float4* sp = reinterpret_cast<const float4*>(ep.stats + row * (W / 64));
+            const float4* sp4 = reinterpret_cast<const float4*>(ep.stats + row * (W / 64));
             float s = 0.f, ss = 0.f;
             for (int i = 0; i < W / 256; ++i) {
-              const float4 t = sp[i];
+              const float4 t = sp4[i];
               s += t.x + t.z;
               ss += t.y + t.w;
             }
@@ -264,25 +279,32 @@ umma_gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           mbar_wait(&tfull_bar[acc], acc_phase);
           tc_fence_after();
 #pragma unroll 1
-          for (int c0 = 0; c0 < 64; c0 += 32) {
+          for (int bi = 0; bi < 2; ++bi) {
+            const int j = 2 * bi + cg;
+            const uint32_t seq = seq_base + (uint32_t)j;
+            const int slot = (int)(seq % Cfg::kRing);
+            const uint32_t ph = (seq / Cfg::kRing) & 1u;
+            uint8_t* sp = epi_smem + slot * Cfg::kSlotBytes;
             uint32_t sh[32], sc[32];
-            tmem_ld_32x32(t_tile + (uint32_t)(cg * 64 + c0), sh);
-            tmem_ld_32x32(t_tile + (uint32_t)(128 + cg * 64 + c0), sc);
-            float hrow[32];
-            tile_to_row_f32(ws.f, lane, hreg, hrow);
-            if (c0 == 0) tile_ldg_f32(ep.res + row0 * ep.ldo + f0 + 32, ep.ldo, rows_valid, lane, hreg);
+            tmem_ld_32x32(t_tile + (uint32_t)(32 * j), sh);
+            tmem_ld_32x32(t_tile + (uint32_t)(128 + 32 * j), sc);
+            mbar_wait(&efull_bar[slot], ph);
+            float4 hv[8];
+            const uint8_t* hrow = sp + r * 128;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) hv[i] = *reinterpret_cast<const float4*>(hrow + ((i ^ (r & 7)) << 4));
             tmem_ld_wait();
-            const float* bsh = ep.bias + n_blk * 256 + cg * 64 + c0;
+            const float* bsh = ep.bias + n_blk * 256 + 32 * j;
             uint32_t pk[16];
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
               const float4 b1 = __ldg(reinterpret_cast<const float4*>(bsh) + i);
               const float4 b2 = __ldg(reinterpret_cast<const float4*>(bsh + 128) + i);
-              float n0_ = (hrow[4 * i] - mean) * rstd, n1_ = (hrow[4 * i + 1] - mean) * rstd;
-              float n2_ = (hrow[4 * i + 2] - mean) * rstd, n3_ = (hrow[4 * i + 3] - mean) * rstd;
+              float n0_ = (hv[i].x - mean) * rstd, n1_ = (hv[i].y - mean) * rstd;
+              float n2_ = (hv[i].z - mean) * rstd, n3_ = (hv[i].w - mean) * rstd;
               if (ep.ln_w != nullptr) {
-                const float4 g = __ldg(reinterpret_cast<const float4*>(ep.ln_w + f0 + c0) + i);
-                const float4 bb = __ldg(reinterpret_cast<const float4*>(ep.ln_b + f0 + c0) + i);
+                const float4 g = __ldg(reinterpret_cast<const float4*>(ep.ln_w + f0 + 32 * j) + i);
+                const float4 bb = __ldg(reinterpret_cast<const float4*>(ep.ln_b + f0 + 32 * j) + i);
                 n0_ = fmaf(n0_, g.x, bb.x); n1_ = fmaf(n1_, g.y, bb.y); n2_ = fmaf(n2_, g.z, bb.z); n3_ = fmaf(n3_, g.w, bb.w);
               }
               const float o0 = fmaf(n0_, 1.0f + (__uint_as_float(sc[4 * i]) + b2.x), __uint_as_float(sh[4 * i]) + b1.x);
@@ -292,25 +314,57 @@ umma_gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
               pk[2 * i] = pack_bf16x2(o0, o1);
               pk[2 * i + 1] = pack_bf16x2(o2, o3);
             }
-            row_stg_b16(ws.b, reinterpret_cast<bf16*>(ep.out) + row0 * ep.ldo + f0 + c0, ep.ldo, rows_valid, lane, pk);
+            uint8_t* orow = sp + Cfg::kSlotH + r * 64;
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+              *reinterpret_cast<uint4*>(orow + ((i ^ rsw) << 4)) = make_uint4(pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
+            fence_proxy_async();
+            named_bar_sync(1 + cg, 128);
+            if (q == 0 && lane == 0) {
+              tma_store_2d(&em.g, sp + Cfg::kSlotH, f0 + 32 * j, r0cta);
+              bulk_commit_group();
+              bulk_wait_read_all();
+              mbar_arrive(&eempty_bar[slot]);
+            }
+            __syncwarp();
           }
+          seq_base += 4;
         } else {
-          // gate tile: bf16 store into out2
-          const int g0 = (n_blk - ep.ln_tiles) * BN + cg * 128;
+          // gate tile: bf16 boxes into out2 (h_out map)
+          const int g0 = (n_blk - ep.ln_tiles) * BN;
           mbar_wait(&tfull_bar[acc], acc_phase);
           tc_fence_after();
 #pragma unroll 1
-          for (int c0 = 0; c0 < 128; c0 += 32) {
+          for (int bi = 0; bi < BN / 64; ++bi) {
+            const int blk = 2 * bi + cg;
+            const uint32_t seq = seq_base + (uint32_t)blk;
+            const int slot = (int)(seq % Cfg::kRing);
+            const uint32_t ph = (seq / Cfg::kRing) & 1u;
+            uint8_t* sp = epi_smem + slot * Cfg::kSlotBytes;
             uint32_t v[32];
-            tmem_ld_32x32(t_tile + (uint32_t)(cg * 128 + c0), v);
+            tmem_ld_32x32(t_tile + (uint32_t)(32 * blk), v);
             float b[32];
-            bias32_ldg(ep.bias + n_blk * 256 + cg * 128 + c0, b);
+            bias32_ldg(ep.bias + n_blk * 256 + 32 * blk, b);
+            mbar_wait(&efull_bar[slot], ph);  // slot free (relayed by the prefetch warp)
             tmem_ld_wait();
             uint32_t pk[16];
 #pragma unroll
             for (int i = 0; i < 16; ++i) pk[i] = pack_bf16x2(__uint_as_float(v[2 * i]) + b[2 * i], __uint_as_float(v[2 * i + 1]) + b[2 * i + 1]);
-            row_stg_b16(ws.b, reinterpret_cast<bf16*>(ep.out2) + row0 * ep.ldo2 + g0 + c0, ep.ldo2, rows_valid, lane, pk);
+            uint8_t* orow = sp + Cfg::kSlotH + r * 64;
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+              *reinterpret_cast<uint4*>(orow + ((i ^ rsw) << 4)) = make_uint4(pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
+            fence_proxy_async();
+            named_bar_sync(1 + cg, 128);
+            if (q == 0 && lane == 0) {
+              tma_store_2d(&em.h_out, sp + Cfg::kSlotH, g0 + 32 * blk, r0cta);
+              bulk_commit_group();
+              bulk_wait_read_all();
+              mbar_arrive(&eempty_bar[slot]);
+            }
+            __syncwarp();
           }
+          seq_base += BN / 32;
         }
       } else if constexpr (KIND == EPI_GATED_RES) {
         // h[rows, cols] = h + gate * (acc + bias) on the fp32 residual stream + row sums for the next LayerNorm.
