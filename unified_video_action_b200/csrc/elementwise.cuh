@@ -91,7 +91,22 @@ constexpr int IP_ROWS = 64;
 __global__ void __launch_bounds__(256)
 k_input_proj(const float* __restrict__ x, const float* __restrict__ Wi, const float* __restrict__ bi,
              float* __restrict__ h, int64_t rows, int C, int W, int64_t half, float* __restrict__ stats) {
+  __shared__ __align__(16) float xs[IP_ROWS][16];  // the block's input rows, zero padded to 16 channels
   const int64_t r0 = (int64_t)blockIdx.x * IP_ROWS;
+  const int64_t left = rows - r0;
+  const int nr = left < IP_ROWS ? (int)left : IP_ROWS;
+  for (int i = threadIdx.x; i < IP_ROWS * 16; i += blockDim.x) {
+    const int rr = i >> 4, c = i & 15;
+    float v = 0.f;
+    if (rr < nr && c < C) {
+      const int64_t r = r0 + rr;
+      const int64_t rs = (half > 0 && r >= half) ? (r - half) : r;  // rows < 2 * half
+      v = __ldg(x + rs * C + c);
+    }
+    xs[rr][c] = v;
+  }
+  __syncthreads();
+  const int lane = threadIdx.x & 31;
   for (int j0 = threadIdx.x * 4; j0 < W; j0 += blockDim.x * 4) {
     float w[4][16];
     float b[4];
@@ -110,35 +125,48 @@ k_input_proj(const float* __restrict__ x, const float* __restrict__ Wi, const fl
         for (int c = 0; c < 16; ++c) w[q][c] = (c < C) ? Wi[(int64_t)(j0 + q) * C + c] : 0.f;
       }
     }
-#pragma unroll 4
-    for (int rr = 0; rr < IP_ROWS; ++rr) {
-      const int64_t r = r0 + rr;
-      if (r >= rows) break;
-      const int64_t rs = (half > 0 && r >= half) ? (r - half) : r;  // rows < 2 * half
-      float xv[16];
-      if (C == 16) {
-        const float4* xp = reinterpret_cast<const float4*>(x + rs * 16);
+    float* hp = h + r0 * W + j0;
+    float* sp = stats != nullptr ? stats + (r0 * (W / 128) + j0 / 128) * 2 : nullptr;
+    // two rows per iteration (independent FMA chains); padded rows compute zeros and are not stored
+#pragma unroll 1
+    for (int rr = 0; rr < nr; rr += 2) {
+      float acc[2][4];
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        const float4* xp = reinterpret_cast<const float4*>(xs[rr + u]);
+        float xv[16];
 #pragma unroll
         for (int c4 = 0; c4 < 4; ++c4) {
-          const float4 t = __ldg(xp + c4);
+          const float4 t = xp[c4];
           xv[4 * c4] = t.x; xv[4 * c4 + 1] = t.y; xv[4 * c4 + 2] = t.z; xv[4 * c4 + 3] = t.w;
         }
-      } else {
 #pragma unroll
-        for (int c = 0; c < 16; ++c) xv[c] = (c < C) ? __ldg(x + rs * C + c) : 0.f;
+        for (int q = 0; q < 4; ++q) acc[u][q] = b[q];
+#pragma unroll
+        for (int c = 0; c < 16; ++c) {
+#pragma unroll
+          for (int q = 0; q < 4; ++q) acc[u][q] = fmaf(xv[c], w[q][c], acc[u][q]);
+        }
       }
-      float acc[4] = {b[0], b[1], b[2], b[3]};
+      const bool two = rr + 1 < nr;  // block-uniform
+      *reinterpret_cast<float4*>(hp + (int64_t)rr * W) = make_float4(acc[0][0], acc[0][1], acc[0][2], acc[0][3]);
+      if (two) *reinterpret_cast<float4*>(hp + (int64_t)(rr + 1) * W) = make_float4(acc[1][0], acc[1][1], acc[1][2], acc[1][3]);
+      if (sp != nullptr) {  // row sums for the LayerNorm of the first block: one (sum, sum of squares) per 128 columns
+        float s0 = (acc[0][0] + acc[0][1]) + (acc[0][2] + acc[0][3]);
+        float q0 = (acc[0][0] * acc[0][0] + acc[0][1] * acc[0][1]) + (acc[0][2] * acc[0][2] + acc[0][3] * acc[0][3]);
+        float s1 = (acc[1][0] + acc[1][1]) + (acc[1][2] + acc[1][3]);
+        float q1 = (acc[1][0] * acc[1][0] + acc[1][1] * acc[1][1]) + (acc[1][2] * acc[1][2] + acc[1][3] * acc[1][3]);
 #pragma unroll
-      for (int c = 0; c < 16; ++c) {
-#pragma unroll
-        for (int q = 0; q < 4; ++q) acc[q] = fmaf(xv[c], w[q][c], acc[q]);
-      }
-      *reinterpret_cast<float4*>(h + r * W + j0) = make_float4(acc[0], acc[1], acc[2], acc[3]);
-      if (stats != nullptr) {  // row sums for the LayerNorm of the first block (uniform branch)
-        const float s = warp_sum((acc[0] + acc[1]) + (acc[2] + acc[3]));
-        const float ss = warp_sum((acc[0] * acc[0] + acc[1] * acc[1]) + (acc[2] * acc[2] + acc[3] * acc[3]));
-        // one (sum, sum of squares) slot per 128 columns = per warp (deterministic, no atomics)
-        if ((threadIdx.x & 31) == 0) *reinterpret_cast<float2*>(stats + (r * (W / 128) + j0 / 128) * 2) = make_float2(s, ss);
+        for (int o = 16; o > 0; o >>= 1) {
+          s0 += __shfl_xor_sync(0xffffffffu, s0, o);
+          q0 += __shfl_xor_sync(0xffffffffu, q0, o);
+          s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+          q1 += __shfl_xor_sync(0xffffffffu, q1, o);
+        }
+        if (lane == 0) {
+          *reinterpret_cast<float2*>(sp + (int64_t)rr * (W / 128) * 2) = make_float2(s0, q0);
+          if (two) *reinterpret_cast<float2*>(sp + (int64_t)(rr + 1) * (W / 128) * 2) = make_float2(s1, q1);
+        }
       }
     }
   }

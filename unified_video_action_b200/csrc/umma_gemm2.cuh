@@ -37,7 +37,8 @@ struct Umma2Cfg {
   static constexpr int kStageBytesA = UG_BM * UG_BK * 2;
   static constexpr int kStageBytesB = kBNH * UG_BK * 2;
   static constexpr int kStageBytes = kStageBytesA + kStageBytesB;
-  static constexpr bool kTmaEpi = (KIND == EPI_GATED_RES || KIND == EPI_LNMOD);
+  static constexpr bool kTmaEpi = (KIND == EPI_GATED_RES || KIND == EPI_LNMOD || KIND == EPI_SILU_ACT || KIND == EPI_STORE_ACT);
+  static constexpr bool kTmaOutOnly = (KIND == EPI_SILU_ACT || KIND == EPI_STORE_ACT);  // ring = output staging only
   static constexpr int kStages = kTmaEpi ? 4 : 5;
   static constexpr int kRing = 4;                         // epilogue prefetch ring (kTmaEpi)
   static constexpr int kSlotH = UG_BM * 32 * 4;           // 16 KB
@@ -217,7 +218,9 @@ umma_gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             const uint32_t ph = (seq / Cfg::kRing) & 1u;
             mbar_wait(&eempty_bar[slot], ph ^ 1u);
             uint8_t* sp = epi_smem + slot * Cfg::kSlotBytes;
-            if constexpr (KIND == EPI_LNMOD) {
+            if constexpr (Cfg::kTmaOutOnly) {
+              mbar_arrive(&efull_bar[slot]);  // relays "slot free" to the epilogue warps
+            } else if constexpr (KIND == EPI_LNMOD) {
               if (ln_tile) {  // residual columns of this tile's 128 features
                 mbar_arrive_expect_tx(&efull_bar[slot], (uint32_t)Cfg::kSlotH);
                 tma_load_2d(sp, &em.h_in, &efull_bar[slot], n_blk * 128 + 32 * blk, r0);
@@ -423,27 +426,48 @@ umma_gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         if (ep.stats != nullptr && row_ok)
           *reinterpret_cast<float2*>(ep.stats + (row * (ep.ln_width / 128) + n_blk * 2 + cg) * 2) = make_float2(s, ss);
       } else if constexpr (KIND == EPI_SILU_ACT || KIND == EPI_STORE_ACT) {
-        bf16* outp = reinterpret_cast<bf16*>(ep.out) + row0 * ep.ldo + n0;
+        // out(bf16) = f(acc + bias): 32-column boxes staged in the ring and written with TMA stores (h_out map)
+        const int r = q * 32 + lane;
+        const int32_t r0cta = (int32_t)(m_blk * BM2) + (int32_t)rank * UG_BM;
+        const uint32_t rsw = (uint32_t)((r >> 1) & 3);
         mbar_wait(&tfull_bar[acc], acc_phase);
         tc_fence_after();
 #pragma unroll 1
-        for (int c0 = 0; c0 < kColsPerGroup; c0 += 32) {
+        for (int bi = 0; bi < BN / 64; ++bi) {
+          const int blk = 2 * bi + cg;
+          const uint32_t seq = tile_seq * (BN / 32) + (uint32_t)blk;
+          const int slot = (int)(seq % Cfg::kRing);
+          const uint32_t ph = (seq / Cfg::kRing) & 1u;
+          uint8_t* sp = epi_smem + slot * Cfg::kSlotBytes;
           uint32_t v[32];
-          tmem_ld_32x32(t_tile + (uint32_t)(cg * kColsPerGroup + c0), v);
+          tmem_ld_32x32(t_tile + (uint32_t)(32 * blk), v);
           float b[32];
-          bias32_ldg(ep.bias != nullptr ? ep.bias + n0 + c0 : nullptr, b);
+          bias32_ldg(ep.bias != nullptr ? ep.bias + n_blk * BN + 32 * blk : nullptr, b);
           tmem_ld_wait();
           uint32_t pk[16];
 #pragma unroll
           for (int i = 0; i < 16; ++i) {
             float x0 = __uint_as_float(v[2 * i]) + b[2 * i], x1 = __uint_as_float(v[2 * i + 1]) + b[2 * i + 1];
             if constexpr (KIND == EPI_SILU_ACT) {
-              x0 = __fdividef(x0, 1.0f + __expf(-x0));
-              x1 = __fdividef(x1, 1.0f + __expf(-x1));
+              x0 = silu_tanh(x0);
+              x1 = silu_tanh(x1);
             }
             pk[i] = pack_bf16x2(x0, x1);
           }
-          row_stg_b16(ws.b, outp + c0, ep.ldo, rows_valid, lane, pk);
+          mbar_wait(&efull_bar[slot], ph);  // slot free (relayed by warp 3)
+          uint8_t* orow = sp + Cfg::kSlotH + r * 64;
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+            *reinterpret_cast<uint4*>(orow + ((i ^ rsw) << 4)) = make_uint4(pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
+          fence_proxy_async();
+          named_bar_sync(1 + cg, 128);
+          if (q == 0 && lane == 0) {
+            tma_store_2d(&em.h_out, sp + Cfg::kSlotH, n_blk * BN + 32 * blk, r0cta);
+            bulk_commit_group();
+            bulk_wait_read_all();
+            mbar_arrive(&eempty_bar[slot]);
+          }
+          __syncwarp();
         }
       } else {
         typename RowEpi<KIND, TA>::Pre pre;
