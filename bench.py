@@ -4,8 +4,14 @@
 Workload (config.workload): BASELINE config 3, "UVA PushT-M multitask inference, 100-step DDPM + CFG
 over all masked tokens, batch 64 per GPU": DiffLoss.sample on 64 x 1024 cond rows || 64 x 1024 uncond
 rows = 131 072 rows per GPU, C=16, cfg=3.0, temperature 0.95, clip_denoised=False, 100 denoise steps.
-One bench "step" = one such sample() call = 13 107 200 row-steps per GPU.  (token-steps/s is a
-sampling metric; configs[1], the training step, is reported by --workload train as rows/s.)
+One bench "step" = one such sample() call = 13 107 200 row-steps per GPU.  token-steps/s is a
+sampling metric, so the sampling config it is quoted on is the default workload; the other
+BASELINE configs are reported as extra keys of the same JSON line at N=1 ("extras": C1 p50
+predict_action head latency, C2 training rows/s) or selected with --workload:
+
+    --workload train     C2: DiffLoss fwd+bwd N=16384 + DiffActLoss fwd+bwd N=256 per GPU, rows/s
+    --workload latency   C1: DiffActLoss.sample B=1 (N=16) and B=56 (N=896), p50 over 200 calls
+    --workload sweep     C5: DiffLoss.sample cfg=1, N = 1k .. 256k rows
 
     python bench.py --gpus 1 --steps 3 --warmup 3
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
@@ -16,8 +22,10 @@ value  : whole-job row-steps/s with z / start noise / step noise already residen
          CUDA events around K library calls (max over ranks).
 e2e    : same metric through the public API DiffLoss.sample(z) with z in pinned HOST memory: the
          H2D copy of z, the RNG draws, the 100-step loop and the D2H copy of the samples are all timed.
-roofline: dominant kernel = the AdaLN-modulation GEMM ([rows,1024] x [1024,20480], 61% of the
-         algorithmic FLOPs), timed live with CUDA event pairs on the launch stream.
+roofline: dominant kernel = the AdaLN-modulation GEMM with the LayerNorm-modulate epilogue
+         (umma_gemm2_kernel<256, EPI_LNMOD>; [rows,1024] x [1024,20480] per denoise step in 7 launches,
+         61% of the algorithmic FLOPs), timed live with CUDA event pairs on its launch stream in a
+         separate pass of the same workload with the two-lane overlap off (so each launch runs alone).
 """
 import argparse
 import json
@@ -35,6 +43,9 @@ C, Z, W, DEPTH, T_GEN = 16, 768, 1024, 6, 100
 CFG, TEMP = 3.0, 0.95
 FLOP_PER_ROW_STEP = 2 * (C * W + DEPTH * 5 * W * W + 2 * W * W + W * 2 * C)  # 67 207 168
 ADA_FLOP_PER_ROW = 2 * (3 * DEPTH + 2) * W * W  # AdaLN modulation GEMM, per row per denoise step
+# dram__bytes_read.sum + dram__bytes_write.sum of one EPI_LNMOD launch (65536 rows x 3072 columns) from the
+# ncu --set full capture in profiles/ (None until captured for the current kernel)
+NCU_TRAFFIC_BYTES = None
 TRAIN_FLOP_PER_ROW = 6 * (C * W + 256 * W + W * W + Z * W + DEPTH * 5 * W * W + 2 * W * W + W * 2 * C)
 
 
@@ -132,6 +143,127 @@ def cpu_sample_rate(rows, steps, seed=0):
     return rows * steps / dt, dt
 
 
+def make_act_head(dev, A=2):
+    """DiffActLoss (PushT: A=2; DAL:12-107) with the zero-initialised tensors re-drawn like make_head."""
+    import torch
+
+    from unified_video_action_b200 import DiffActLoss
+
+    torch.manual_seed(1)
+    head = DiffActLoss(A, Z, DEPTH, W, str(T_GEN), n_frames=4, language_emb_model=None, language_emb_model_type=None)
+    g = torch.Generator().manual_seed(1)
+    with torch.no_grad():
+        for n, p in head.named_parameters():
+            if "adaLN_modulation" in n or n.startswith("net.final_layer.linear"):
+                p.copy_(0.02 * torch.randn(p.shape, generator=g))
+    return head.to(dev)
+
+
+def _p50(xs):
+    xs = sorted(xs)
+    return xs[len(xs) // 2]
+
+
+def measure_latency(dev, batches=(1, 56), calls=200):
+    """C1: p50 wall-clock latency of DiffActLoss.sample(z[B,1024,768]) (pre-net + RNG draws + 100-step
+    DDPM loop, clip_denoised=True, cfg=1) with z on the device and the actions read back to the host,
+    i.e. the head's share of predict_action (MAR:1037-1041)."""
+    import torch
+
+    head = make_act_head(dev)
+    out = {}
+    for B in batches:
+        z = torch.randn(B, 1024, Z, device=dev)
+        for _ in range(5):
+            head.sample(z, temperature=TEMP, cfg=1.0).cpu()
+        ts = []
+        l0 = head.net.head().launch_count()
+        for _ in range(calls):
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            head.sample(z, temperature=TEMP, cfg=1.0).cpu()
+            ts.append((time.perf_counter() - t0) * 1e3)
+        launches = (head.net.head().launch_count() - l0) / calls
+        ts.sort()
+        out[f"B{B}_rows{16 * B}"] = {"p50_ms": ts[len(ts) // 2], "p90_ms": ts[int(len(ts) * 0.9)], "calls": calls,
+                                    "row_steps_per_s": 16 * B * T_GEN / (ts[len(ts) // 2] / 1e3),
+                                    "launches_per_call": launches}
+    return out
+
+
+def measure_train(dev, world, B=16, iters=5, warmup=2):
+    """C2: one joint training step of the two heads (full_dynamic_model case): DiffLoss fwd+bwd on
+    B x 1024 rows + DiffActLoss fwd+bwd on B x 16 rows, bf16 GEMMs, gradients wrt z and every head
+    parameter; with world > 1 the head gradients are all-reduced over NCCL.  Returns rows/s
+    per GPU and ms per step (CUDA events)."""
+    import torch
+    import torch.distributed as dist
+
+    from unified_video_action_b200 import allreduce_head_grads
+
+    vid, act = make_head(dev), make_act_head(dev)
+    g = torch.Generator(device=dev).manual_seed(4321)
+    z = torch.randn(B, 1024, Z, generator=g, device=dev, requires_grad=True)
+    target = 0.2325 * torch.randn(B, 1024, C, generator=g, device=dev)
+    mask = (torch.rand(B, 1024, generator=g, device=dev) < 0.85).float()
+    actions = torch.rand(B, 16, 2, generator=g, device=dev) * 2 - 1
+
+    def step():
+        for m in (vid, act):
+            for p in m.parameters():
+                p.grad = None
+        z.grad = None
+        loss = vid(target, z, mask) + act(actions, z)
+        loss.backward()
+        if world > 1:
+            allreduce_head_grads([vid, act])
+        return loss
+
+    for _ in range(warmup):
+        step()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        loss = step()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / iters
+    rows = B * 1024 + B * 16
+    return {"ms_per_step": ms, "rows_per_gpu": rows, "rows_per_s_per_gpu": rows / (ms / 1e3),
+            "tflops_per_gpu": (B * 1024) * TRAIN_FLOP_PER_ROW / (ms / 1e3) / 1e12, "loss": float(loss.detach()),
+            "what": f"DiffLoss fwd+bwd {B}x1024 rows + DiffActLoss fwd+bwd {B}x16 rows (incl. its PyTorch pre-net), bf16"}
+
+
+def measure_sweep(dev, sizes=(1024, 2048, 4096, 8192, 16384, 32768, 65536, 131072, 262144), dsteps=T_GEN):
+    """C5: DiffLoss.sample, cfg=1, N = 1k .. 256k rows: row-steps/s per size (device-resident inputs)."""
+    import torch
+
+    lib_head = make_head(dev).net.head()
+    out = {}
+    for n in sizes:
+        g = torch.Generator(device=dev).manual_seed(n)
+        z = torch.randn(n, Z, generator=g, device=dev)
+        x0 = torch.randn(n, C, generator=g, device=dev)
+        nz = torch.randn(dsteps, n, C, generator=g, device=dev)
+        f = lambda: lib_head.sample(z, x0, nz, temperature=TEMP, cfg=1.0, clip_denoised=False, k_begin=0, k_end=dsteps)
+        f()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        reps = 3 if n <= 32768 else 1
+        e0.record()
+        for _ in range(reps):
+            f()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / reps
+        out[str(n)] = {"ms": ms, "row_steps_per_s": n * dsteps / (ms / 1e3)}
+        del z, x0, nz
+    return out
+
+
 def run_reference(args):
     """--impl reference: the reference's CPU implementation of the path (oracle port: the reference
     is Python and cannot travel to the GPU box), all host threads, bounded sample per step."""
@@ -141,7 +273,7 @@ def run_reference(args):
     if rank != 0:
         return
     cores = torch.get_num_threads()
-    rows, dsteps = 1024, 2
+    rows, dsteps = 2048, 20
     for _ in range(args.warmup):
         cpu_sample_rate(256, 1)
     rates, times = [], []
@@ -150,7 +282,7 @@ def run_reference(args):
         rates.append(r)
         times.append(dt)
     total = rows * dsteps * args.steps / sum(times)
-    sample = f"{rows} rows (512 cond || 512 uncond) x {dsteps} of the 100 denoise steps per bench step, fp32 torch CPU"
+    sample = f"{rows} rows ({rows // 2} cond || {rows // 2} uncond) x {dsteps} of the 100 denoise steps per bench step, fp32 torch CPU"
     line = {
         "impl": "reference", "metric": "diffusion-head token-steps/sec", "value": total, "unit": "row-steps/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * sum(times) / args.steps,
@@ -170,10 +302,12 @@ def main():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="sample", choices=["sample", "train", "latency", "sweep"])
     ap.add_argument("--rows", type=int, default=131072, help="rows per GPU (cond || uncond)")
     ap.add_argument("--denoise-steps", type=int, default=T_GEN)
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the C1 latency / C2 training extras of the default line")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
@@ -190,6 +324,34 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     os.environ["UVA_B200_PRECISION"] = args.precision
+
+    if args.workload != "sample":
+        if args.workload == "train":
+            res = measure_train(dev, world, iters=max(args.steps, 1), warmup=max(args.warmup, 1))
+            t = torch.tensor([res["ms_per_step"]], device=dev, dtype=torch.float64)
+            if world > 1:
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            res["ms_per_step"] = float(t.item())
+            line = {"metric": "diffusion-head training rows/sec (fwd+bwd)", "unit": "rows/s", "n_gpus": world,
+                    "value": world * res["rows_per_gpu"] / (res["ms_per_step"] / 1e3), "ms_per_step": res["ms_per_step"],
+                    "higher_is_better": True, "scaling": "weak", "dtype": args.precision, "data": "synthetic",
+                    "config": {"workload": "C2: " + res["what"], "collective": "flat fp32 all-reduce of head grads" if world > 1 else "none"},
+                    "detail": res}
+        elif args.workload == "latency":
+            line = {"metric": "p50 predict_action head latency", "unit": "ms", "n_gpus": 1, "higher_is_better": False,
+                    "dtype": args.precision, "data": "synthetic",
+                    "config": {"workload": "C1: DiffActLoss.sample, z [B,1024,768] on device, A=2, 100 steps, clip_denoised"},
+                    "detail": measure_latency(dev)} if rank == 0 else None
+        else:
+            line = {"metric": "diffusion-head token-steps/sec", "unit": "row-steps/s", "n_gpus": 1, "higher_is_better": True,
+                    "dtype": args.precision, "data": "synthetic", "config": {"workload": "C5: DiffLoss.sample cfg=1, N sweep"},
+                    "detail": measure_sweep(dev, dsteps=args.denoise_steps)} if rank == 0 else None
+        if rank == 0 and line is not None:
+            print(json.dumps(line), flush=True)
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
     head = make_head(dev)
     lib_head = head.net.head()
     rows, K, Wm, dsteps = args.rows, args.steps, max(args.warmup, 0), args.denoise_steps
@@ -205,13 +367,12 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    def call():
-        return lib_head.sample(z, x0, step_noise, temperature=TEMP, cfg=CFG, clip_denoised=False, k_begin=0, k_end=dsteps)
+    def call(k_end=dsteps):
+        return lib_head.sample(z, x0, step_noise, temperature=TEMP, cfg=CFG, clip_denoised=False, k_begin=0, k_end=k_end)
 
     for _ in range(Wm):
         call()
     barrier()
-    lib_head.timing_enable(True)
     l0 = lib_head.launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     with ClockSampler(local) as clk:
@@ -223,16 +384,23 @@ def main():
         barrier()
     ms = e0.elapsed_time(e1)
     launches = lib_head.launch_count() - l0
-    lib_head.timing_enable(False)
-    ada_ms, ada_n = lib_head.timing_read(0)
-    for cat in (1, 2, 3, 4):
-        lib_head.timing_read(cat)
     assert torch.isfinite(out).all(), "non-finite samples"
     t = torch.tensor([ms], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms = float(t.item())
     value = world * rows * dsteps * K / (ms / 1e3)
+
+    # ---- roofline pass: the dominant kernel timed alone (event pairs around every launch, one lane) ----
+    rsteps = min(dsteps, 10)
+    lib_head.timing_enable(True)
+    call(rsteps)
+    torch.cuda.synchronize()
+    lib_head.timing_enable(False)
+    ada_ms, ada_n = lib_head.timing_read(0)
+    cat_ms = {0: ada_ms}
+    for cat in (1, 2, 3, 4):
+        cat_ms[cat], _ = lib_head.timing_read(cat)
 
     # ---- e2e through the public API, host buffers ----
     z_host = z.cpu().pin_memory()
@@ -246,6 +414,7 @@ def main():
 
     e2e = None
     if dsteps == T_GEN:
+        del step_noise
         call_e2e()
         barrier()
         e0.record()
@@ -261,7 +430,7 @@ def main():
 
     if rank == 0:
         burst, sustained, src = _peaks()
-        ada_tflops = (ADA_FLOP_PER_ROW * rows * dsteps * K / (ada_ms / 1e3) / 1e12) if ada_ms > 0 else None
+        ada_tflops = (ADA_FLOP_PER_ROW * rows * rsteps / (ada_ms / 1e3) / 1e12) if ada_ms > 0 else None
         line = {
             "metric": "diffusion-head token-steps/sec", "value": value, "unit": "row-steps/s", "n_gpus": world,
             "steps": K, "warmup": Wm, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak",
@@ -271,19 +440,26 @@ def main():
                        "l2": "inputs larger than L2 (z 403 MB, step noise 839 MB per call)", "parallelism": f"rows x{world}"},
             "e2e": e2e, "gpu_launches": int(launches),
             "roofline": {"bound": "tensor", "achieved": ada_tflops, "peak": sustained, "unit": "TFLOP/s",
-                         "frac": (ada_tflops / sustained) if ada_tflops else None, "traffic": None,
-                         "kernel": "umma_gemm_tn_kernel<256, EPI_STORE_ACT> (AdaLN modulation GEMM)",
+                         "frac": (ada_tflops / sustained) if ada_tflops else None, "traffic": NCU_TRAFFIC_BYTES,
+                         "kernel": "umma_gemm2_kernel<256, EPI_LNMOD> (AdaLN modulation GEMM + LayerNorm-modulate epilogue)",
                          "launches_timed": int(ada_n), "avg_launch_ms": (ada_ms / ada_n) if ada_n else None,
+                         "flop_per_launch_avg": ADA_FLOP_PER_ROW * rows * rsteps / ada_n if ada_n else None,
+                         "share_of_gemm_time": ada_ms / sum(cat_ms.values()) if ada_ms > 0 else None,
+                         "timed": f"{rsteps} denoise steps, chunks one after the other, CUDA event pair per launch",
                          "peak_source": f"MEASURED_PEAKS.json bf16_tflops_sustained ({src}); burst {burst}"},
             "step_tflops": value / world * FLOP_PER_ROW_STEP / 1e12,
             "step_frac_of_burst_peak": value / world * FLOP_PER_ROW_STEP / 1e12 / burst,
             "clocks": clk.summary(),
         }
         if not args.no_cpu_baseline and world == 1:
-            crow, csteps = 512, 3
+            crow, csteps = 2048, 50
             rate, dt = cpu_sample_rate(crow, csteps)
             line["cpu_baseline"] = {"value": rate, "unit": "row-steps/s", "cores": torch.get_num_threads(), "kind": "port",
                                     "sample": f"{crow} rows x {csteps} denoise steps of the same CFG workload ({dt:.1f} s), fp32 torch CPU oracle port"}
+        if not args.no_extras and world == 1 and dsteps == T_GEN:
+            del z, x0, z_dev
+            torch.cuda.empty_cache()
+            line["extras"] = {"C1_latency": measure_latency(dev, calls=100), "C2_train": measure_train(dev, 1)}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

@@ -137,7 +137,9 @@ int64_t uva_head_launch_count(const UvaHead* h);
 /* Optional per-kernel timing for the roofline report: while enabled, every tcgen05 GEMM launch is
  * bracketed by CUDA events on the launch stream.  timing_read synchronises on the recorded events of
  * one category (0 AdaLN-modulation GEMM, 1 MLP GEMM 1, 2 MLP GEMM 2, 3 final linear, 4 cond_embed),
- * returns their summed duration and count, and forgets them. */
+ * returns their summed duration and count, and forgets them.  While timing is enabled the sampler
+ * runs its row chunks one after the other (no two-lane overlap), so each timed kernel has the GPU
+ * to itself. */
 int uva_head_timing_enable(UvaHead* h, int32_t enable);
 int uva_head_timing_read(UvaHead* h, int32_t category, double* total_ms, int64_t* count);
 
