@@ -81,6 +81,29 @@ __global__ void k_ysilu(const float* __restrict__ cemb, const float* __restrict_
   }
 }
 
+// The same for a group of denoise steps at once (latency path: the condition embedding does not change
+// over the chain, so SiLU(c + temb[t_k]) of every step k is known up front): ys[(g, r), :] for step
+// k0 + g, g < G; tsteps[k] = original-process timestep of loop iteration k.
+__global__ void k_ysilu_steps(const float* __restrict__ cemb, const float* __restrict__ temb,
+                              const int* __restrict__ tsteps, int k0, int G, bf16* __restrict__ ys,
+                              int64_t rows, int W) {
+  const int wq = W / 4;
+  const int64_t per = rows * wq;
+  const int64_t n = per * G;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int g = (int)(i / per);
+    const int64_t rem = i - (int64_t)g * per;
+    const int64_t r = rem / wq;
+    const int j = (int)(rem - r * wq) * 4;
+    const int64_t t = tsteps[k0 + g];
+    const float4 c = *reinterpret_cast<const float4*>(cemb + r * W + j);
+    const float4 e = __ldg(reinterpret_cast<const float4*>(temb + t * W + j));
+    bf16 o[4] = {__float2bfloat16_rn(silu_f(c.x + e.x)), __float2bfloat16_rn(silu_f(c.y + e.y)),
+                 __float2bfloat16_rn(silu_f(c.z + e.z)), __float2bfloat16_rn(silu_f(c.w + e.w))};
+    *reinterpret_cast<uint2*>(ys + ((int64_t)g * rows + r) * W + j) = *reinterpret_cast<uint2*>(o);
+  }
+}
+
 // ------------------------------------------------------------------------------------------
 // input_proj (DL:233, 268): h[r, :] = x[src(r), :] . Wi^T + bi,  K = C <= 16 (CUDA cores, fp32:
 // the diffusion state is never rounded to bf16).  With CFG (half > 0) the net input of row r is

@@ -171,6 +171,17 @@ struct UvaHead {
   bool fuse_ln = true;  // UVA_FUSE_LN: LayerNorm-modulate inside the AdaLN GEMM epilogue (bf16 sampling path)
   int grid_mult = 1;  // UVA_GRID_MULT: GEMM grids of grid_mult x #SMs CTAs (block scheduler balances the tail)
   int dbg_skip = 0;  // UVA_DEBUG_SKIP (timing diagnosis only, results are wrong): 1 = no GEMM launches, 2 = no row kernels
+  // latency path (head_small.inc): small batches run with the AdaLN modulation of all denoise steps
+  // computed up front and the whole chain replayed from a CUDA graph
+  int* d_tsteps = nullptr;       // [T_gen] original-process timestep of loop iteration k
+  int64_t small_rows = 1024;     // UVA_SMALL_ROWS: largest batch that takes the latency path
+  bool use_graph = true;         // UVA_GRAPH
+  bool bn32 = true;              // UVA_BN32: 128 x 32 tiles for the W x W GEMMs when rows <= 128 (32 CTAs stream the weight)
+  struct SmallGraph {
+    const void* ws; int64_t N; int k_begin, k_end, clip; float temperature, cfg;
+    cudaGraphExec_t exec; int64_t launches; int seen;
+  };
+  std::vector<SmallGraph> graphs;
   bool timing = false;
   int cur_cat = 0;
   struct TimedLaunch { int cat; cudaEvent_t a, b; };
@@ -273,6 +284,9 @@ extern "C" int uva_head_create(const UvaHeadDesc* desc, UvaHead** out) {
   if (const char* e = getenv("UVA_QUAD")) h->quad = atoi(e) != 0;
   if (const char* e = getenv("UVA_FUSE_LN")) h->fuse_ln = atoi(e) != 0;
   if (const char* e = getenv("UVA_DEBUG_SKIP")) h->dbg_skip = atoi(e);
+  if (const char* e = getenv("UVA_SMALL_ROWS")) h->small_rows = atol(e);
+  if (const char* e = getenv("UVA_GRAPH")) h->use_graph = atoi(e) != 0;
+  if (const char* e = getenv("UVA_BN32")) h->bn32 = atoi(e) != 0;
   if (const char* e = getenv("UVA_GRID_MULT")) { int v = atoi(e); if (v >= 1 && v <= 64) h->grid_mult = v; }
   CUDA_TRY(cudaStreamCreateWithFlags(&h->side, cudaStreamNonBlocking));
   CUDA_TRY(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
@@ -281,6 +295,12 @@ extern "C" int uva_head_create(const UvaHeadDesc* desc, UvaHead** out) {
   h->train = create_schedule(d.T_train, d.T_train);
   int rc = upload_tables(h->train, h->dtrain, &h->d_tables);
   if (rc != UVA_OK) { delete h; return rc; }
+  {
+    std::vector<int> ts(d.T_gen);
+    for (int k = 0; k < d.T_gen; ++k) ts[k] = h->gen.timestep_map[d.T_gen - 1 - k];  // GD:519 order, RS:122-127 map
+    CUDA_TRY(cudaMalloc(&h->d_tsteps, ts.size() * sizeof(int)));
+    CUDA_TRY(cudaMemcpy(h->d_tsteps, ts.data(), ts.size() * sizeof(int), cudaMemcpyHostToDevice));
+  }
 
   // sinusoidal features for t = 0..T_train-1 (DL:110-134): cos || sin of t * freqs (fp32 args)
   {
@@ -345,7 +365,9 @@ extern "C" int uva_head_create(const UvaHeadDesc* desc, UvaHead** out) {
 extern "C" void uva_head_destroy(UvaHead* h) {
   if (!h) return;
   cudaFree(h->d_tables); cudaFree(h->feat); cudaFree(h->temb); cudaFree(h->temb_hidden); cudaFree(h->temb_pre);
-  cudaFree(h->wf); cudaFree(h->wb); cudaFree(h->adab_p);
+  cudaFree(h->wf); cudaFree(h->wb); cudaFree(h->adab_p); cudaFree(h->d_tsteps);
+  for (auto& g : h->graphs)
+    if (g.exec) cudaGraphExecDestroy(g.exec);
   if (h->side) cudaStreamDestroy(h->side);
   if (h->ev_fork) cudaEventDestroy(h->ev_fork);
   if (h->ev_join) cudaEventDestroy(h->ev_join);
@@ -353,5 +375,6 @@ extern "C" void uva_head_destroy(UvaHead* h) {
 }
 
 #include "head_infer.inc"
+#include "head_small.inc"
 #include "head_sample.inc"
 #include "head_train.inc"
