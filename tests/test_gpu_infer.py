@@ -251,11 +251,11 @@ def test_action_head_clip_chain(golden_dir, mode, tol_end):
     assert float((out - ref).abs().max()) <= tol_end * max(1.0, float(ref.abs().max()))
 
 
-@pytest.mark.parametrize("N,cfg,clip,k_end", [(16, 1.0, True, 100), (112, 1.0, True, 23), (896, 1.0, False, 12), (64, 3.0, False, 30)])
+@pytest.mark.parametrize("N,cfg,clip,k_end", [(16, 1.0, True, 100), (27, 1.0, True, 23), (112, 1.0, True, 23), (896, 1.0, False, 12), (32, 3.0, False, 30)])
 def test_latency_path_equals_chunked_path(video, monkeypatch, N, cfg, clip, k_end):
-    """Small batches take the latency path (modulation tables of all steps hoisted into one GEMM, chain
-    replayed from a CUDA graph): eager call, capturing call and replay give the same samples, and they
-    agree with the general chunked path (same kernels for the chain, different tiling of the AdaLN GEMM)."""
+    """Small batches take the latency path (modulation tables of all steps hoisted into one GEMM; N <= 128:
+    one persistent cooperative chain kernel, else the chain replayed from a CUDA graph): repeated calls
+    (eager, capturing, replay) give the same samples, and they agree with the general chunked path."""
     dev, g, P = video
     gen = torch.Generator().manual_seed(N + k_end)
     z = torch.randn(N, 768, generator=gen)
@@ -271,7 +271,10 @@ def test_latency_path_equals_chunked_path(video, monkeypatch, N, cfg, clip, k_en
     l0 = h.launch_count()
     outs = [h.sample(*args, **kw).cpu() for _ in range(3)]
     per_call = (h.launch_count() - l0) / 3
-    assert per_call > 10 * k_end  # the replayed graph's kernels are counted
+    if N > 32:
+        assert per_call > 10 * k_end  # the replayed graph's kernels are counted
+    else:
+        assert per_call < 12  # persistent chain kernel: a handful of launches per call
     assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2])
     monkeypatch.setenv("UVA_SMALL_ROWS", "0")
     hg = _head(16, 768, 1024, 6, P, 1, dev)

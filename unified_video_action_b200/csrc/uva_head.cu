@@ -20,6 +20,7 @@
 #include "train_kernels.cuh"
 #include "umma_gemm.cuh"
 #include "umma_gemm2.cuh"
+#include "chain_kernel.cuh"
 
 using namespace uva;
 
@@ -175,6 +176,9 @@ struct UvaHead {
   // computed up front and the whole chain replayed from a CUDA graph
   int* d_tsteps = nullptr;       // [T_gen] original-process timestep of loop iteration k
   int64_t small_rows = 1024;     // UVA_SMALL_ROWS: largest batch that takes the latency path
+  StepCoef* d_coef = nullptr;    // [T_gen] DDPM update coefficients of the sampling process, by timestep index
+  bool use_chain = true;         // UVA_CHAIN: persistent chain kernel (chain_kernel.cuh)
+  int64_t chain_rows = 32;       // UVA_CHAIN_ROWS: largest batch it takes (its time grows with rows / 16)
   bool use_graph = true;         // UVA_GRAPH
   bool bn32 = true;              // UVA_BN32: 128 x 32 tiles for the W x W GEMMs when rows <= 128 (32 CTAs stream the weight)
   struct SmallGraph {
@@ -286,6 +290,8 @@ extern "C" int uva_head_create(const UvaHeadDesc* desc, UvaHead** out) {
   if (const char* e = getenv("UVA_DEBUG_SKIP")) h->dbg_skip = atoi(e);
   if (const char* e = getenv("UVA_SMALL_ROWS")) h->small_rows = atol(e);
   if (const char* e = getenv("UVA_GRAPH")) h->use_graph = atoi(e) != 0;
+  if (const char* e = getenv("UVA_CHAIN")) h->use_chain = atoi(e) != 0;
+  if (const char* e = getenv("UVA_CHAIN_ROWS")) { long v = atol(e); if (v >= 1 && v <= 128) h->chain_rows = v; }
   if (const char* e = getenv("UVA_BN32")) h->bn32 = atoi(e) != 0;
   if (const char* e = getenv("UVA_GRID_MULT")) { int v = atoi(e); if (v >= 1 && v <= 64) h->grid_mult = v; }
   CUDA_TRY(cudaStreamCreateWithFlags(&h->side, cudaStreamNonBlocking));
@@ -300,6 +306,18 @@ extern "C" int uva_head_create(const UvaHeadDesc* desc, UvaHead** out) {
     for (int k = 0; k < d.T_gen; ++k) ts[k] = h->gen.timestep_map[d.T_gen - 1 - k];  // GD:519 order, RS:122-127 map
     CUDA_TRY(cudaMalloc(&h->d_tsteps, ts.size() * sizeof(int)));
     CUDA_TRY(cudaMemcpy(h->d_tsteps, ts.data(), ts.size() * sizeof(int), cudaMemcpyHostToDevice));
+    std::vector<StepCoef> kc(d.T_gen);
+    for (int i = 0; i < d.T_gen; ++i) {  // .float() of the float64 tables at use (GD:901)
+      kc[i].sqrt_recip = (float)h->gen.sqrt_recip_alphas_cumprod[i];
+      kc[i].sqrt_recipm1 = (float)h->gen.sqrt_recipm1_alphas_cumprod[i];
+      kc[i].coef1 = (float)h->gen.posterior_mean_coef1[i];
+      kc[i].coef2 = (float)h->gen.posterior_mean_coef2[i];
+      kc[i].min_log = (float)h->gen.posterior_log_variance_clipped[i];
+      kc[i].max_log = (float)h->gen.log_betas[i];
+      kc[i].nonzero = (i != 0) ? 1 : 0;
+    }
+    CUDA_TRY(cudaMalloc(&h->d_coef, kc.size() * sizeof(StepCoef)));
+    CUDA_TRY(cudaMemcpy(h->d_coef, kc.data(), kc.size() * sizeof(StepCoef), cudaMemcpyHostToDevice));
   }
 
   // sinusoidal features for t = 0..T_train-1 (DL:110-134): cos || sin of t * freqs (fp32 args)
@@ -365,7 +383,7 @@ extern "C" int uva_head_create(const UvaHeadDesc* desc, UvaHead** out) {
 extern "C" void uva_head_destroy(UvaHead* h) {
   if (!h) return;
   cudaFree(h->d_tables); cudaFree(h->feat); cudaFree(h->temb); cudaFree(h->temb_hidden); cudaFree(h->temb_pre);
-  cudaFree(h->wf); cudaFree(h->wb); cudaFree(h->adab_p); cudaFree(h->d_tsteps);
+  cudaFree(h->wf); cudaFree(h->wb); cudaFree(h->adab_p); cudaFree(h->d_tsteps); cudaFree(h->d_coef);
   for (auto& g : h->graphs)
     if (g.exec) cudaGraphExecDestroy(g.exec);
   if (h->side) cudaStreamDestroy(h->side);
