@@ -45,7 +45,7 @@ FLOP_PER_ROW_STEP = 2 * (C * W + DEPTH * 5 * W * W + 2 * W * W + W * 2 * C)  # 6
 ADA_FLOP_PER_ROW = 2 * (3 * DEPTH + 2) * W * W  # AdaLN modulation GEMM, per row per denoise step
 # dram__bytes_read.sum + dram__bytes_write.sum of one EPI_LNMOD launch (65536 rows x 3072 columns) from the
 # ncu --set full capture in profiles/ (None until captured for the current kernel)
-NCU_TRAFFIC_BYTES = None
+NCU_TRAFFIC_BYTES = 654.1e6  # profiles/r01_ncu_full_gemm2_v4_summary.txt: 413.8 MB read + 240.3 MB written
 TRAIN_FLOP_PER_ROW = 6 * (C * W + 256 * W + W * W + Z * W + DEPTH * 5 * W * W + 2 * W * W + W * 2 * C)
 
 
@@ -272,6 +272,10 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    try:  # torchrun exports OMP_NUM_THREADS=1: the CPU arm uses every host core this process may run on
+        torch.set_num_threads(len(os.sched_getaffinity(0)))
+    except Exception:
+        pass
     cores = torch.get_num_threads()
     rows, dsteps = 2048, 20
     for _ in range(args.warmup):
@@ -439,20 +443,25 @@ def main():
                        "rows_per_gpu": rows, "denoise_steps": dsteps, "cfg": CFG, "temperature": TEMP,
                        "l2": "inputs larger than L2 (z 403 MB, step noise 839 MB per call)", "parallelism": f"rows x{world}"},
             "e2e": e2e, "gpu_launches": int(launches),
-            "roofline": {"bound": "tensor", "achieved": ada_tflops, "peak": sustained, "unit": "TFLOP/s",
-                         "frac": (ada_tflops / sustained) if ada_tflops else None, "traffic": NCU_TRAFFIC_BYTES,
+            "roofline": {"bound": "tensor", "achieved": ada_tflops, "peak": burst, "unit": "TFLOP/s",
+                         "frac": (ada_tflops / burst) if ada_tflops else None, "traffic": NCU_TRAFFIC_BYTES,
+                         "traffic_note": "ncu dram bytes of one 65536-row x 3072-column launch; algorithmic bytes of that launch: 671 MB (ys + h read, a + gate written)",
                          "kernel": "umma_gemm2_kernel<256, EPI_LNMOD> (AdaLN modulation GEMM + LayerNorm-modulate epilogue)",
                          "launches_timed": int(ada_n), "avg_launch_ms": (ada_ms / ada_n) if ada_n else None,
                          "flop_per_launch_avg": ADA_FLOP_PER_ROW * rows * rsteps / ada_n if ada_n else None,
                          "share_of_gemm_time": ada_ms / sum(cat_ms.values()) if ada_ms > 0 else None,
                          "timed": f"{rsteps} denoise steps, chunks one after the other, CUDA event pair per launch",
-                         "peak_source": f"MEASURED_PEAKS.json bf16_tflops_sustained ({src}); burst {burst}"},
+                         "peak_source": f"MEASURED_PEAKS.json bf16_tflops burst ({src}) because the kernel is timed alone in a short pass; sustained {sustained}"},
             "step_tflops": value / world * FLOP_PER_ROW_STEP / 1e12,
             "step_frac_of_burst_peak": value / world * FLOP_PER_ROW_STEP / 1e12 / burst,
             "clocks": clk.summary(),
         }
         if not args.no_cpu_baseline and world == 1:
             crow, csteps = 2048, 50
+            try:
+                torch.set_num_threads(len(os.sched_getaffinity(0)))
+            except Exception:
+                pass
             rate, dt = cpu_sample_rate(crow, csteps)
             line["cpu_baseline"] = {"value": rate, "unit": "row-steps/s", "cores": torch.get_num_threads(), "kind": "port",
                                     "sample": f"{crow} rows x {csteps} denoise steps of the same CFG workload ({dt:.1f} s), fp32 torch CPU oracle port"}
