@@ -277,34 +277,64 @@ k_lnmod_bwd_generic(const TA* __restrict__ da, const float* __restrict__ h, cons
 }
 
 // ------------------------------------------------------------------------------------------
-// Column sums (bias gradients): out[c] += sum_r X[r, c].  Block = 32 column quads x 8 row lanes,
-// FW_ROWS*4 rows per block.
+// Column sums (bias gradients): out[c] += sum_r X[r, c].  A block covers CS_ROWS rows x (32 lanes x
+// 16 bytes) columns; warp w takes rows w, w + 8, ... with 8 independent 16-byte loads in flight per lane,
+// the 8 warps are combined through shared memory and added with one atomic per column.
 // ------------------------------------------------------------------------------------------
+constexpr int CS_ROWS = 256;
 template <typename TI>
 __global__ void __launch_bounds__(256)
 k_colsum(const TI* __restrict__ X, int64_t ld, int64_t rows, int cols, float* __restrict__ out) {
-  __shared__ float red[8][128 + 4];
-  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-  const int c0 = (blockIdx.x * 32 + tx) * 4;
-  const int64_t r0 = (int64_t)blockIdx.y * (FW_ROWS * 4);
-  const int64_t r1 = (r0 + FW_ROWS * 4 < rows) ? r0 + FW_ROWS * 4 : rows;
-  float s[4] = {0.f, 0.f, 0.f, 0.f};
-  if (c0 < cols) {
-    for (int64_t r = r0 + ty; r < r1; r += 8) {
-      float v[4];
-      load4<TI>(X + r * ld + c0, v);
-      s[0] += v[0]; s[1] += v[1]; s[2] += v[2]; s[3] += v[3];
+  constexpr int EPL = 16 / (int)sizeof(TI);  // elements per lane
+  __shared__ float red[8][32 * EPL + 4];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int c0 = (blockIdx.x * 32 + lane) * EPL;
+  const int64_t r0 = (int64_t)blockIdx.y * CS_ROWS;
+  const int64_t r1 = (r0 + CS_ROWS < rows) ? r0 + CS_ROWS : rows;
+  float s[EPL];
+#pragma unroll
+  for (int q = 0; q < EPL; ++q) s[q] = 0.f;
+  if (c0 + EPL <= cols) {
+    const TI* base = X + c0;
+    int64_t r = r0 + w;
+    for (; r + 56 < r1; r += 64) {
+      uint4 v[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) v[u] = *reinterpret_cast<const uint4*>(base + (r + 8 * u) * ld);
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        if constexpr (sizeof(TI) == 2) {
+          const __nv_bfloat162* p2 = reinterpret_cast<const __nv_bfloat162*>(&v[u]);
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const float2 f = __bfloat1622float2(p2[q]);
+            s[2 * q] += f.x;
+            s[2 * q + 1] += f.y;
+          }
+        } else {
+          const float* pf = reinterpret_cast<const float*>(&v[u]);
+#pragma unroll
+          for (int q = 0; q < EPL; ++q) s[q] += pf[q];
+        }
+      }
     }
+    for (; r < r1; r += 8) {
+#pragma unroll
+      for (int q = 0; q < EPL; ++q) s[q] += to_f32(base[r * ld + q]);
+    }
+  } else if (c0 < cols) {  // ragged column tail
+    for (int64_t r = r0 + w; r < r1; r += 8)
+      for (int q = 0; q < EPL && c0 + q < cols; ++q) s[q] += to_f32(X[r * ld + c0 + q]);
   }
 #pragma unroll
-  for (int q = 0; q < 4; ++q) red[ty][tx * 4 + q] = s[q];
+  for (int q = 0; q < EPL; ++q) red[w][lane * EPL + q] = s[q];
   __syncthreads();
-  if (threadIdx.x < 128) {
-    const int c = blockIdx.x * 128 + threadIdx.x;
+  for (int i = threadIdx.x; i < 32 * EPL; i += 256) {
+    const int c = blockIdx.x * 32 * EPL + i;
     if (c < cols) {
       float t = 0.f;
 #pragma unroll
-      for (int w8 = 0; w8 < 8; ++w8) t += red[w8][threadIdx.x];
+      for (int w8 = 0; w8 < 8; ++w8) t += red[w8][i];
       atomicAdd(out + c, t);
     }
   }

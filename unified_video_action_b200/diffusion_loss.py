@@ -195,8 +195,13 @@ class _FusedLoss(torch.autograd.Function):
         net = ctx.net
         head = net.head()
         params = net.ordered_params()
-        grads = [torch.zeros_like(p, dtype=torch.float32, memory_format=torch.contiguous_format)
-                 if p.requires_grad else None for p in params]
+        # one zero-filled flat buffer, one view per parameter (a single memset instead of one fill per tensor)
+        sizes = [(p.numel() + 3) // 4 * 4 if p.requires_grad else 0 for p in params]
+        flat = torch.zeros(sum(sizes), dtype=torch.float32, device=z.device)
+        grads, off = [], 0
+        for p, n in zip(params, sizes):
+            grads.append(flat[off:off + p.numel()].view(p.shape) if p.requires_grad else None)
+            off += n
         dz = head.loss_bwd(dloss.float(), target, z, mask if ctx.has_mask else None, t, noise, grads)
         return (None, None, dz.to(ctx.z_dtype) if ctx.needs_input_grad[2] else None, None, None, None, *grads)
 
