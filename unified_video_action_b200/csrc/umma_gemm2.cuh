@@ -29,6 +29,9 @@ struct EpiMaps {
   CUtensorMap h_in;   // fp32 [M, W], box 32 x 128, 128-byte swizzle (residual stream input)
   CUtensorMap h_out;  // GATED_RES: fp32 output, same geometry as h_in.  LNMOD: bf16 gate output [M, W], 64-byte swizzle
   CUtensorMap g;      // GATED_RES: bf16 gate input [M, N], box 32 x 128, 64-byte swizzle.  LNMOD: bf16 `a` output [M, W]
+  CUtensorMap b2;     // GATED_SAVE: bf16 output of the un-gated MLP result q
+  // training kinds: DSILU_ACT g = aux input, h_out = bf16 output; SILU_SAVE h_out = out, g = out2 (both bf16);
+  // GATED_SAVE h_in = res, h_out = out (fp32), g = gate input, b2 = out2
 };
 
 template <int BN, int KIND = 0>
@@ -37,8 +40,9 @@ struct Umma2Cfg {
   static constexpr int kStageBytesA = UG_BM * UG_BK * 2;
   static constexpr int kStageBytesB = kBNH * UG_BK * 2;
   static constexpr int kStageBytes = kStageBytesA + kStageBytesB;
-  static constexpr bool kTmaEpi = (KIND == EPI_GATED_RES || KIND == EPI_LNMOD || KIND == EPI_SILU_ACT || KIND == EPI_STORE_ACT);
-  static constexpr bool kTmaOutOnly = (KIND == EPI_SILU_ACT || KIND == EPI_STORE_ACT);  // ring = output staging only
+  static constexpr bool kTmaEpi = (KIND == EPI_GATED_RES || KIND == EPI_LNMOD || KIND == EPI_SILU_ACT || KIND == EPI_STORE_ACT ||
+                                   KIND == EPI_DSILU_ACT || KIND == EPI_SILU_SAVE || KIND == EPI_GATED_SAVE);
+  static constexpr bool kTmaOutOnly = (KIND == EPI_SILU_ACT || KIND == EPI_STORE_ACT || KIND == EPI_SILU_SAVE);  // ring = output staging only
   static constexpr int kStages = kTmaEpi ? 4 : 5;
   static constexpr int kRing = 4;                         // epilogue prefetch ring (kTmaEpi)
   static constexpr int kSlotH = UG_BM * 32 * 4;           // 16 KB
@@ -102,6 +106,7 @@ umma_gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       tma_prefetch_desc(&em.h_in);
       tma_prefetch_desc(&em.h_out);
       tma_prefetch_desc(&em.g);
+      if constexpr (KIND == EPI_GATED_SAVE) tma_prefetch_desc(&em.b2);
     }
   }
   if (warp == 1 && lane == 0) {
@@ -227,6 +232,9 @@ umma_gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
               } else {
                 mbar_arrive(&efull_bar[slot]);  // gate tile: the slot is only an output staging buffer
               }
+            } else if constexpr (KIND == EPI_DSILU_ACT) {
+              mbar_arrive_expect_tx(&efull_bar[slot], (uint32_t)Cfg::kSlotG);
+              tma_load_2d(sp + Cfg::kSlotH, &em.g, &efull_bar[slot], c0 + 32 * blk, r0);
             } else {
               mbar_arrive_expect_tx(&efull_bar[slot], (uint32_t)Cfg::kSlotBytes);
               tma_load_2d(sp, &em.h_in, &efull_bar[slot], c0 + 32 * blk, r0);
@@ -463,6 +471,100 @@ umma_gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           named_bar_sync(1 + cg, 128);
           if (q == 0 && lane == 0) {
             tma_store_2d(&em.h_out, sp + Cfg::kSlotH, n_blk * BN + 32 * blk, r0cta);
+            bulk_commit_group();
+            bulk_wait_read_all();
+            mbar_arrive(&eempty_bar[slot]);
+          }
+          __syncwarp();
+        }
+      } else if constexpr (KIND == EPI_DSILU_ACT || KIND == EPI_SILU_SAVE || KIND == EPI_GATED_SAVE) {
+        // training kinds on the same ring (32-column boxes, warp group cg takes blk = cg, cg + 2, ...):
+        //   DSILU_ACT : out(bf16) = acc * SiLU'(aux)            aux box prefetched (g map), result in place
+        //   SILU_SAVE : out2 = p = acc + bias, out = SiLU(p)      two bf16 output boxes (g part: out, h part: out2)
+        //   GATED_SAVE: q = acc + bias -> out2(bf16); out(f32) = res + gate * q   (res / gate prefetched)
+        const int r = q * 32 + lane;
+        const int32_t r0cta = (int32_t)(m_blk * BM2) + (int32_t)rank * UG_BM;
+        const uint32_t rsw = (uint32_t)((r >> 1) & 3);
+        mbar_wait(&tfull_bar[acc], acc_phase);
+        tc_fence_after();
+#pragma unroll 1
+        for (int bi = 0; bi < BN / 64; ++bi) {
+          const int blk = 2 * bi + cg;
+          const uint32_t seq = tile_seq * (BN / 32) + (uint32_t)blk;
+          const int slot = (int)(seq % Cfg::kRing);
+          const uint32_t ph = (seq / Cfg::kRing) & 1u;
+          uint8_t* sp = epi_smem + slot * Cfg::kSlotBytes;
+          uint8_t* grow = sp + Cfg::kSlotH + r * 64;
+          uint32_t v[32];
+          tmem_ld_32x32(t_tile + (uint32_t)(32 * blk), v);
+          float b[32];
+          bias32_ldg((KIND != EPI_DSILU_ACT && ep.bias != nullptr) ? ep.bias + n_blk * BN + 32 * blk : nullptr, b);
+          mbar_wait(&efull_bar[slot], ph);
+          uint32_t pk[16];
+          if constexpr (KIND == EPI_DSILU_ACT) {
+            uint4 av[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) av[i] = *reinterpret_cast<const uint4*>(grow + ((i ^ rsw) << 4));
+            tmem_ld_wait();
+            const uint32_t* aw = reinterpret_cast<const uint32_t*>(av);
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+              const float2 pq = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&aw[i]));
+              pk[i] = pack_bf16x2(__uint_as_float(v[2 * i]) * dsilu_f(pq.x), __uint_as_float(v[2 * i + 1]) * dsilu_f(pq.y));
+            }
+          } else if constexpr (KIND == EPI_SILU_SAVE) {
+            tmem_ld_wait();
+            uint32_t pp[16];
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+              const float x0 = __uint_as_float(v[2 * i]) + b[2 * i], x1 = __uint_as_float(v[2 * i + 1]) + b[2 * i + 1];
+              pp[i] = pack_bf16x2(x0, x1);
+              pk[i] = pack_bf16x2(silu_f(x0), silu_f(x1));
+            }
+            uint8_t* prow = sp + r * 64;  // first 8 KB of the h part: the pre-activation box
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+              *reinterpret_cast<uint4*>(prow + ((i ^ rsw) << 4)) = make_uint4(pp[4 * i], pp[4 * i + 1], pp[4 * i + 2], pp[4 * i + 3]);
+          } else {
+            float4 hv[8];
+            uint4 gv[4];
+            uint8_t* hrow = sp + r * 128;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) hv[i] = *reinterpret_cast<const float4*>(hrow + ((i ^ (r & 7)) << 4));
+#pragma unroll
+            for (int i = 0; i < 4; ++i) gv[i] = *reinterpret_cast<const uint4*>(grow + ((i ^ rsw) << 4));
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              const uint4 gq = gv[i >> 1];
+              const uint32_t w0 = (i & 1) ? gq.z : gq.x, w1 = (i & 1) ? gq.w : gq.y;
+              const float2 ga = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w0));
+              const float2 gb = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w1));
+              const float q0 = __uint_as_float(v[4 * i]) + b[4 * i], q1 = __uint_as_float(v[4 * i + 1]) + b[4 * i + 1];
+              const float q2 = __uint_as_float(v[4 * i + 2]) + b[4 * i + 2], q3 = __uint_as_float(v[4 * i + 3]) + b[4 * i + 3];
+              pk[2 * i] = pack_bf16x2(q0, q1);
+              pk[2 * i + 1] = pack_bf16x2(q2, q3);
+              float4 o = hv[i];
+              o.x = fmaf(ga.x, q0, o.x); o.y = fmaf(ga.y, q1, o.y); o.z = fmaf(gb.x, q2, o.z); o.w = fmaf(gb.y, q3, o.w);
+              *reinterpret_cast<float4*>(hrow + ((i ^ (r & 7)) << 4)) = o;
+            }
+          }
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+            *reinterpret_cast<uint4*>(grow + ((i ^ rsw) << 4)) = make_uint4(pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
+          fence_proxy_async();
+          named_bar_sync(1 + cg, 128);
+          if (q == 0 && lane == 0) {
+            const int32_t cc = n_blk * BN + 32 * blk;
+            if constexpr (KIND == EPI_DSILU_ACT) {
+              tma_store_2d(&em.h_out, sp + Cfg::kSlotH, cc, r0cta);
+            } else if constexpr (KIND == EPI_SILU_SAVE) {
+              tma_store_2d(&em.h_out, sp + Cfg::kSlotH, cc, r0cta);
+              tma_store_2d(&em.g, sp, cc, r0cta);
+            } else {
+              tma_store_2d(&em.h_out, sp, cc, r0cta);
+              tma_store_2d(&em.b2, sp + Cfg::kSlotH, cc, r0cta);
+            }
             bulk_commit_group();
             bulk_wait_read_all();
             mbar_arrive(&eempty_bar[slot]);

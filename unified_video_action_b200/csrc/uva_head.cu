@@ -146,6 +146,8 @@ struct UvaHead {
   float* temb = nullptr;      // [T_train, W] TimestepEmbedder(t) table
   float* temb_hidden = nullptr;  // [T_train, W] SiLU(Linear0(feat)) (kept for the backward)
   float* temb_pre = nullptr;     // [T_train, W] Linear0(feat) before the SiLU (kept for the backward)
+  bf16 *temb_hidden_b = nullptr, *temb_pre_b = nullptr, *feat_b = nullptr;  // bf16 copies: operands of the backward GEMMs (bf16 mode)
+  size_t ob_te2w = 0;            // bf16 copy of time_embed.mlp.2.weight [W, W]
   // fp32 parameter copy, own layout (offsets in floats)
   float* wf = nullptr;
   size_t wf_floats = 0;
@@ -337,6 +339,13 @@ extern "C" int uva_head_create(const UvaHeadDesc* desc, UvaHead** out) {
     CUDA_TRY(cudaMalloc(&h->temb, (size_t)d.T_train * d.W * sizeof(float)));
     CUDA_TRY(cudaMalloc(&h->temb_hidden, (size_t)d.T_train * d.W * sizeof(float)));
     CUDA_TRY(cudaMalloc(&h->temb_pre, (size_t)d.T_train * d.W * sizeof(float)));
+    if (d.mode == UVA_MODE_BF16) {
+      CUDA_TRY(cudaMalloc(&h->temb_hidden_b, (size_t)d.T_train * d.W * sizeof(bf16)));
+      CUDA_TRY(cudaMalloc(&h->temb_pre_b, (size_t)d.T_train * d.W * sizeof(bf16)));
+      CUDA_TRY(cudaMalloc(&h->feat_b, f.size() * sizeof(bf16)));
+      k_convert<bf16><<<grid_for((int64_t)f.size(), 256, h->num_sms), 256>>>(h->feat, h->feat_b, (int64_t)f.size());
+      CUDA_TRY(cudaDeviceSynchronize());
+    }
   }
 
   // fp32 parameter layout
@@ -363,6 +372,7 @@ extern "C" int uva_head_create(const UvaHeadDesc* desc, UvaHead** out) {
     auto take = [&](size_t n) { size_t r = o; o += (n + 511) / 512 * 512; return r; };
     h->ob_condw = take(W * Z); h->ob_adaw = take((size_t)h->nmod * W); h->ob_linw = take(32 * W);
     h->ob_adaw_p = take((size_t)h->nmod * W);
+    h->ob_te2w = take(W * W);
     CUDA_TRY(cudaMalloc(&h->adab_p, (size_t)h->nmod * sizeof(float)));
     for (int b = 0; b < d.depth; ++b) {
       h->ob_w1.push_back(take(W * W)); h->ob_w2.push_back(take(W * W));
@@ -383,6 +393,7 @@ extern "C" int uva_head_create(const UvaHeadDesc* desc, UvaHead** out) {
 extern "C" void uva_head_destroy(UvaHead* h) {
   if (!h) return;
   cudaFree(h->d_tables); cudaFree(h->feat); cudaFree(h->temb); cudaFree(h->temb_hidden); cudaFree(h->temb_pre);
+  cudaFree(h->temb_hidden_b); cudaFree(h->temb_pre_b); cudaFree(h->feat_b);
   cudaFree(h->wf); cudaFree(h->wb); cudaFree(h->adab_p); cudaFree(h->d_tsteps); cudaFree(h->d_coef);
   for (auto& g : h->graphs)
     if (g.exec) cudaGraphExecDestroy(g.exec);
