@@ -46,6 +46,26 @@ def _worker(rank, world, port, out_dir):
                 p.grad = (rank + 1.0) * b.clone()
         n = allreduce_head_grads(heads)
         assert n == len(heads)
+        # the fused backward hands out views of one flat buffer: those are reduced in place (no packing)
+        net_params = list(heads[0].net.parameters())
+        flat = torch.zeros(sum((p.numel() + 3) // 4 * 4 for p in net_params))
+        off, views = 0, []
+        for p in net_params:
+            v = flat[off:off + p.numel()].view(p.shape)
+            v.copy_((rank + 1.0) * torch.ones_like(p))
+            p.grad = v
+            views.append(v)
+            off += (p.numel() + 3) // 4 * 4
+        assert allreduce_head_grads([heads[0]]) == 1
+        for p, v in zip(net_params, views):
+            assert p.grad.data_ptr() == v.data_ptr()
+            torch.testing.assert_close(p.grad, torch.full_like(p, sum(r + 1.0 for r in range(world)) / world))
+        # restore the synthetic gradients checked below
+        i = 0
+        for h in heads:
+            for p in h.parameters():
+                p.grad = (sum(r + 1.0 for r in range(world)) / world) * base[i].clone()
+                i += 1
         want = sum(r + 1.0 for r in range(world)) / world
         i = 0
         for h in heads:

@@ -57,9 +57,28 @@ def shard_rows(n_rows: int, rank: int, world_size: int, pair_halves: bool = Fals
     return begin, begin + base + (1 if rank < rem else 0)
 
 
+def _shared_flat(grads):
+    """If every gradient is a contiguous view into one storage (what ``_FusedLoss.backward`` produces),
+    return a 1-D tensor over the span they occupy; else None.  Gaps of the span hold alignment padding
+    (zeros), which an all-reduce leaves harmlessly summed."""
+    g0 = grads[0]
+    st = g0.untyped_storage()
+    lo, hi = None, None
+    for g in grads:
+        if g.dtype != g0.dtype or not g.is_contiguous() or g.untyped_storage().data_ptr() != st.data_ptr():
+            return None
+        b, e = g.storage_offset(), g.storage_offset() + g.numel()
+        lo = b if lo is None else min(lo, b)
+        hi = e if hi is None else max(hi, e)
+    if hi - lo > 2 * sum(g.numel() for g in grads):
+        return None
+    return torch.empty(0, dtype=g0.dtype, device=g0.device).set_(st, lo, (hi - lo,))
+
+
 def allreduce_head_grads(heads: Iterable[nn.Module], group=None, average: bool = True) -> int:
-    """Data-parallel training: one all-reduce per head over a flat fp32 gradient buffer (NCCL over
-    NVLink on GPUs, gloo in the CPU tests).  Returns the number of collectives issued."""
+    """Data-parallel training: all-reduce of the head gradients over flat fp32 buffers (NCCL over NVLink
+    on GPUs, gloo in the CPU tests): one collective per flat gradient buffer of the fused backward plus
+    one for any other gradients of the head.  Returns the number of collectives issued."""
     import torch.distributed as dist
 
     n = 0
@@ -68,13 +87,29 @@ def allreduce_head_grads(heads: Iterable[nn.Module], group=None, average: bool =
         grads = [p.grad for p in head.parameters() if p.grad is not None]
         if not grads:
             continue
-        flat = torch.cat([g.reshape(-1) for g in grads])
-        dist.all_reduce(flat, group=group)
-        if average:
-            flat /= world
-        off = 0
+        # gradients that are views of one flat buffer (what the fused backward hands out) are reduced in
+        # place; the others (e.g. the PyTorch pre-net of DiffActLoss) are packed into one buffer
+        groups = {}
         for g in grads:
-            g.copy_(flat[off:off + g.numel()].view_as(g))
-            off += g.numel()
-        n += 1
+            groups.setdefault(g.untyped_storage().data_ptr(), []).append(g)
+        loose = []
+        for members in groups.values():
+            flat = _shared_flat(members) if len(members) > 1 else None
+            if flat is None:
+                loose.extend(members)
+                continue
+            dist.all_reduce(flat, group=group)
+            if average:
+                flat /= world
+            n += 1
+        if loose:
+            flat = torch.cat([g.reshape(-1) for g in loose])
+            dist.all_reduce(flat, group=group)
+            if average:
+                flat /= world
+            off = 0
+            for g in loose:
+                g.copy_(flat[off:off + g.numel()].view_as(g))
+                off += g.numel()
+            n += 1
     return n
