@@ -264,11 +264,22 @@ def test_module_forward_backward_matches_oracle(video):
     rl, _, rdz, rg = _oracle(P, target.reshape(-1, 16).cpu(), z.detach().reshape(-1, 768).cpu(), mask.reshape(-1).cpu(),
                              t.cpu(), noise.cpu())
     assert loss.dim() == 0
-    assert abs(float(loss) - float(rl)) <= FP32_TOL * abs(float(rl))
+    assert abs(float(loss.detach()) - float(rl)) <= FP32_TOL * abs(float(rl))
     _check(z.grad.reshape(-1, 768).cpu(), rdz, 0, "dz")
     for k, p in head.net.named_parameters():
         assert p.grad is not None, k
         _check(p.grad.cpu(), rg[k], 0, k)
+    # the fused backward hands out views of one flat buffer; autograd keeps them as .grad, which is what
+    # lets allreduce_head_grads reduce the head's gradients in place with one collective
+    from unified_video_action_b200.patch import _shared_flat
+
+    flat = _shared_flat([p.grad for p in head.net.parameters()])
+    assert flat is not None and flat.numel() >= sum(p.numel() for p in head.net.parameters())
+    # a second backward accumulates into the same tensors (no aliasing surprises)
+    g0 = head.net.cond_embed.weight.grad.clone()
+    torch.manual_seed(77)
+    head(target, z, mask).backward()
+    assert float((head.net.cond_embed.weight.grad - 2 * g0).abs().max()) <= 1e-5 * float(g0.abs().max())
 
 
 def test_error_paths(video):

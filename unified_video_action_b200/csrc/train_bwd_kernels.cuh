@@ -68,11 +68,29 @@ k_final_wgrad(const float* __restrict__ dnet, int ldn, const TA* __restrict__ a,
 #pragma unroll
   for (int c = 0; c < 32; ++c) acc[c] = 0.f;
   if (j < W) {
-    for (int64_t r = r0; r < r1; ++r) {
-      const float av = to_f32(a[r * W + j]);
+    if ((ldn & 3) == 0) {  // vector loads of the dnet row (warp-uniform address: one 16-byte broadcast per 4 FMAs)
+#pragma unroll 2
+      for (int64_t r = r0; r < r1; ++r) {
+        const float av = to_f32(a[r * W + j]);
+        const float4* dp4 = reinterpret_cast<const float4*>(dnet + r * ldn);
 #pragma unroll
-      for (int c = 0; c < 32; ++c)
-        if (c < C2) acc[c] = fmaf(dnet[r * ldn + c], av, acc[c]);
+        for (int c4 = 0; c4 < 8; ++c4) {
+          if (4 * c4 < C2) {
+            const float4 d = __ldg(dp4 + c4);
+            acc[4 * c4] = fmaf(d.x, av, acc[4 * c4]);
+            acc[4 * c4 + 1] = fmaf(d.y, av, acc[4 * c4 + 1]);
+            acc[4 * c4 + 2] = fmaf(d.z, av, acc[4 * c4 + 2]);
+            acc[4 * c4 + 3] = fmaf(d.w, av, acc[4 * c4 + 3]);
+          }
+        }
+      }
+    } else {
+      for (int64_t r = r0; r < r1; ++r) {
+        const float av = to_f32(a[r * W + j]);
+#pragma unroll
+        for (int c = 0; c < 32; ++c)
+          if (c < C2) acc[c] = fmaf(dnet[r * ldn + c], av, acc[c]);
+      }
     }
 #pragma unroll
     for (int c = 0; c < 32; ++c)
@@ -100,12 +118,29 @@ k_inproj_wgrad(const float* __restrict__ dh, const float* __restrict__ xt, float
 #pragma unroll
   for (int c = 0; c < 16; ++c) acc[c] = 0.f;
   float sb = 0.f;
-  for (int64_t r = r0; r < r1; ++r) {
-    const float d = dh[r * W + j];
-    sb += d;
+  if (C == 16) {
+#pragma unroll 2
+    for (int64_t r = r0; r < r1; ++r) {
+      const float d = dh[r * W + j];
+      sb += d;
+      const float4* xp = reinterpret_cast<const float4*>(xt + r * 16);
 #pragma unroll
-    for (int c = 0; c < 16; ++c)
-      if (c < C) acc[c] = fmaf(d, xt[r * C + c], acc[c]);
+      for (int c4 = 0; c4 < 4; ++c4) {
+        const float4 x = __ldg(xp + c4);
+        acc[4 * c4] = fmaf(d, x.x, acc[4 * c4]);
+        acc[4 * c4 + 1] = fmaf(d, x.y, acc[4 * c4 + 1]);
+        acc[4 * c4 + 2] = fmaf(d, x.z, acc[4 * c4 + 2]);
+        acc[4 * c4 + 3] = fmaf(d, x.w, acc[4 * c4 + 3]);
+      }
+    }
+  } else {
+    for (int64_t r = r0; r < r1; ++r) {
+      const float d = dh[r * W + j];
+      sb += d;
+#pragma unroll
+      for (int c = 0; c < 16; ++c)
+        if (c < C) acc[c] = fmaf(d, xt[r * C + c], acc[c]);
+    }
   }
   if (dWi) {
 #pragma unroll
