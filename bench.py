@@ -232,7 +232,24 @@ def measure_train(dev, world, B=16, iters=5, warmup=2):
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / iters
     rows = B * 1024 + B * 16
-    return {"ms_per_step": ms, "rows_per_gpu": rows, "rows_per_s_per_gpu": rows / (ms / 1e3),
+    # optimizer + EMA + operand re-pack of both heads: fused AdamW/EMA pass, then load_weights
+    import copy
+
+    from unified_video_action_b200 import HeadAdamW
+
+    opt = HeadAdamW([vid, act], lr=1e-4, betas=(0.9, 0.95), weight_decay=0.0, ema_modules=[copy.deepcopy(vid), copy.deepcopy(act)])
+    step()
+    opt.step(); vid.net.head(); act.net.head()
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(iters):
+        opt.step()
+        vid.net.head()
+        act.net.head()
+    e1.record()
+    torch.cuda.synchronize()
+    opt_ms = e0.elapsed_time(e1) / iters
+    return {"ms_per_step": ms, "optimizer_ema_repack_ms": opt_ms, "rows_per_gpu": rows, "rows_per_s_per_gpu": rows / (ms / 1e3),
             "tflops_per_gpu": (B * 1024) * TRAIN_FLOP_PER_ROW / (ms / 1e3) / 1e12, "loss": float(loss.detach()),
             "what": f"DiffLoss fwd+bwd {B}x1024 rows + DiffActLoss fwd+bwd {B}x16 rows (incl. its PyTorch pre-net), bf16"}
 

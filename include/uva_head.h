@@ -131,6 +131,23 @@ int uva_head_loss_bwd(UvaHead* h, const float* dloss, const float* target, const
                       float* dz, float* const* dparams /*host array of device ptrs*/,
                       void* ws, size_t ws_bytes, void* stream);
 
+/* Fused AdamW + EMA update of a list of fp32 parameter tensors in ONE pass.  Replaces
+ * torch.optim.AdamW.step() as configured by the reference (policy/unified_video_action_policy.py:325-360:
+ * decoupled weight decay, 0 on 1-D tensors and biases) followed by EMAModel.step()
+ * (model/autoregressive/ema_model.py:58-89).  Per tensor t (host arrays of device pointers):
+ *   g = grads[t] * grad_scale;  p *= 1 - lr * weight_decay[t];  m = beta1 m + (1 - beta1) g;
+ *   v = beta2 v + (1 - beta2) g^2;  p -= lr / (1 - beta1^step) * m / (sqrt(v) / sqrt(1 - beta2^step) + eps);
+ *   ema[t] = ema[t] * ema_decay + p * (1 - ema_decay)      (skipped when ema == NULL or ema[t] == NULL)
+ * step is the 1-based count of this update.  Call uva_head_load_weights afterwards to refresh the packed
+ * operands. */
+typedef struct {
+  float lr, beta1, beta2, eps, ema_decay, grad_scale;
+  int32_t step;
+} UvaAdamWHyper;
+int uva_adamw_ema_step(int32_t n_tensors, float* const* params, const float* const* grads,
+                       float* const* exp_avg, float* const* exp_avg_sq, float* const* ema,
+                       const int64_t* numel, const float* weight_decay, const UvaAdamWHyper* hp, void* stream);
+
 /* Number of kernel launches this handle has enqueued so far (bench.py's gpu_launches). */
 int64_t uva_head_launch_count(const UvaHead* h);
 

@@ -509,3 +509,38 @@ def training_flops_per_row(C: int, Z: int = 768, W: int = 1024, depth: int = 6, 
     """fwd+bwd FLOP per row = 3 x 2 x MACs as executed by the reference."""
     macs = C * W + freq * W + W * W + Z * W + depth * (5 * W * W) + 2 * W * W + W * 2 * C
     return 6 * macs
+
+
+# ------------------------------------------------------------------------------------------------
+# Optimizer / EMA step for the head parameters (SURVEY.md 8f-2)
+# ------------------------------------------------------------------------------------------------
+def ema_get_decay(optimization_step: int, update_after_step=0, inv_gamma=1.0, power=2 / 3, min_value=0.0,
+                  max_value=0.9999) -> float:
+    """EMAModel.get_decay (model/autoregressive/ema_model.py:46-56)."""
+    step = max(0, optimization_step - update_after_step - 1)
+    value = 1 - (1 + step / inv_gamma) ** -power
+    if step <= 0:
+        return 0.0
+    return max(min_value, min(value, max_value))
+
+
+def adamw_ema_step(params, grads, exp_avg, exp_avg_sq, ema, weight_decay, lr, betas, eps, step, ema_decay,
+                   grad_scale=1.0):
+    """One torch.optim.AdamW update (amsgrad=False; the optimizer the reference builds in
+    policy/unified_video_action_policy.py:343-360 with the decay groups of :325-341), written out
+    tensor by tensor in the order of torch's single-tensor implementation, followed by
+    EMAModel.step (ema_model.py:58-89): ema = ema * decay + p * (1 - decay).  All lists are torch CPU
+    fp32 tensors updated IN PLACE; ``step`` is the 1-based count of this update; ``ema`` may be None."""
+    b1, b2 = betas
+    bc1 = 1 - b1 ** step
+    bc2_sqrt = (1 - b2 ** step) ** 0.5
+    for i, p in enumerate(params):
+        g = grads[i] * grad_scale
+        p.mul_(1 - lr * weight_decay[i])
+        exp_avg[i].lerp_(g, 1 - b1)
+        exp_avg_sq[i].mul_(b2).addcmul_(g, g, value=1 - b2)
+        denom = (exp_avg_sq[i].sqrt() / bc2_sqrt).add_(eps)
+        p.addcdiv_(exp_avg[i], denom, value=-(lr / bc1))
+        if ema is not None and ema[i] is not None:
+            ema[i].mul_(ema_decay)
+            ema[i].add_(p, alpha=1 - ema_decay)

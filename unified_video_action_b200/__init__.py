@@ -8,5 +8,6 @@ PyTorch; ``patch(mar_model)`` swaps the heads of a reference ``MAR`` in place.
 from .diffusion_loss import DiffLoss, SimpleMLPAdaLN, param_names  # noqa: F401
 from .diffusion_action_loss import DiffActLoss  # noqa: F401
 from .patch import patch, shard_rows, allreduce_head_grads  # noqa: F401
+from .optim import HeadAdamW, ema_decay_at  # noqa: F401
 
-__all__ = ["DiffLoss", "DiffActLoss", "SimpleMLPAdaLN", "param_names", "patch", "shard_rows", "allreduce_head_grads"]
+__all__ = ["DiffLoss", "DiffActLoss", "SimpleMLPAdaLN", "param_names", "patch", "shard_rows", "allreduce_head_grads", "HeadAdamW", "ema_decay_at"]

@@ -73,6 +73,7 @@ SYMBOLS = [
     "uva_schedule_table", "uva_head_load_weights", "uva_head_workspace_bytes", "uva_head_net_forward",
     "uva_head_sample", "uva_head_loss_fwd", "uva_head_loss_bwd", "uva_head_launch_count",
     "uva_gemm_bf16_selftest", "uva_last_error", "uva_build_info", "uva_head_timing_enable", "uva_head_timing_read",
+    "uva_adamw_ema_step",
 ]
 
 
@@ -115,6 +116,8 @@ def lib() -> ctypes.CDLL:
         L.uva_head_timing_enable.argtypes = [vp, i32]
         L.uva_head_timing_read.restype = ctypes.c_int
         L.uva_head_timing_read.argtypes = [vp, i32, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(i64)]
+        L.uva_adamw_ema_step.restype = ctypes.c_int
+        L.uva_adamw_ema_step.argtypes = [i32, vp, vp, vp, vp, vp, vp, vp, vp, vp]
         L.uva_last_error.restype = ctypes.c_char_p
         L.uva_build_info.restype = ctypes.c_char_p
         _lib = L

@@ -4,6 +4,7 @@
 // CUDA kernels or fails.
 #include "../../include/uva_head.h"
 
+#include <cmath>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
@@ -21,6 +22,7 @@
 #include "umma_gemm.cuh"
 #include "umma_gemm2.cuh"
 #include "chain_kernel.cuh"
+#include "optim.cuh"
 
 using namespace uva;
 
@@ -401,6 +403,52 @@ extern "C" void uva_head_destroy(UvaHead* h) {
   if (h->ev_fork) cudaEventDestroy(h->ev_fork);
   if (h->ev_join) cudaEventDestroy(h->ev_join);
   delete h;
+}
+
+// ----------------------------------------------------------------------------------------------
+// fused AdamW + EMA step (optim.cuh)
+// ----------------------------------------------------------------------------------------------
+extern "C" int uva_adamw_ema_step(int32_t n_tensors, float* const* params, const float* const* grads,
+                                  float* const* exp_avg, float* const* exp_avg_sq, float* const* ema,
+                                  const int64_t* numel, const float* weight_decay, const UvaAdamWHyper* hp,
+                                  void* stream) {
+  if (n_tensors < 0 || !params || !grads || !exp_avg || !exp_avg_sq || !numel || !weight_decay || !hp)
+    return fail(UVA_ERR_INVALID, "adamw_ema_step: null argument");
+  if (hp->step < 1) return fail(UVA_ERR_INVALID, "adamw_ema_step: step must be >= 1 (it is the 1-based count of this update)");
+  if (!(hp->beta1 >= 0.f && hp->beta1 < 1.f && hp->beta2 >= 0.f && hp->beta2 < 1.f && hp->eps >= 0.f))
+    return fail(UVA_ERR_INVALID, "adamw_ema_step: bad hyper-parameters");
+  cudaStream_t st = (cudaStream_t)stream;
+  int num_sms = 148;
+  {
+    int dev = 0;
+    CUDA_TRY(cudaGetDevice(&dev));
+    CUDA_TRY(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev));
+  }
+  for (int t0 = 0; t0 < n_tensors; t0 += OPT_MAX_TENSORS) {
+    AdamWBatch b = {};
+    b.count = (n_tensors - t0 < OPT_MAX_TENSORS) ? n_tensors - t0 : OPT_MAX_TENSORS;
+    int64_t biggest = 0;
+    for (int i = 0; i < b.count; ++i) {
+      const int t = t0 + i;
+      if (!params[t] || !grads[t] || !exp_avg[t] || !exp_avg_sq[t] || numel[t] < 0)
+        return fail(UVA_ERR_INVALID, "adamw_ema_step: tensor %d has a null pointer or a negative size", t);
+      b.p[i] = params[t]; b.g[i] = grads[t]; b.m[i] = exp_avg[t]; b.v[i] = exp_avg_sq[t];
+      b.ema[i] = ema ? ema[t] : nullptr;
+      b.n[i] = numel[t]; b.wd[i] = weight_decay[t];
+      if (numel[t] > biggest) biggest = numel[t];
+    }
+    b.lr = hp->lr; b.beta1 = hp->beta1; b.beta2 = hp->beta2; b.eps = hp->eps; b.ema_decay = hp->ema_decay;
+    b.grad_scale = hp->grad_scale;
+    b.bc1 = (float)(1.0 - std::pow((double)hp->beta1, (double)hp->step));
+    b.bc2_sqrt = (float)std::sqrt(1.0 - std::pow((double)hp->beta2, (double)hp->step));
+    int bx = (int)((biggest / 4 + 255) / 256);
+    if (bx > 2 * num_sms) bx = 2 * num_sms;
+    if (bx < 1) bx = 1;
+    k_adamw_ema<<<dim3((unsigned)bx, (unsigned)b.count), 256, 0, st>>>(b);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(UVA_ERR_CUDA, "adamw_ema_step: launch failed: %s", cudaGetErrorString(e));
+  }
+  return UVA_OK;
 }
 
 #include "head_infer.inc"
