@@ -202,6 +202,7 @@ def measure_train(dev, world, B=16, iters=5, warmup=2):
     from unified_video_action_b200 import allreduce_head_grads
 
     vid, act = make_head(dev), make_act_head(dev)
+    act.overlap_with(vid)  # what patch() sets up inside a MAR: the action head runs beside the video head
     g = torch.Generator(device=dev).manual_seed(4321)
     z = torch.randn(B, 1024, Z, generator=g, device=dev, requires_grad=True)
     target = 0.2325 * torch.randn(B, 1024, C, generator=g, device=dev)

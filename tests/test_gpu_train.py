@@ -282,6 +282,61 @@ def test_module_forward_backward_matches_oracle(video):
     assert float((head.net.cond_embed.weight.grad - 2 * g0).abs().max()) <= 1e-5 * float(g0.abs().max())
 
 
+def test_action_head_side_stream_equals_serial(video, monkeypatch):
+    """The joint step of MAR.forward_loss (MAR:770-784): video loss + action loss, one backward.  The action
+    head (pre-net, fused loss and, through autograd, their backward) runs on a side stream forked from the
+    entry of the video head; losses, dz and every gradient must equal the single-stream run (same RNG
+    draws: the generator advances in host call order, not in stream order)."""
+    dev, _, P = video
+    import copy
+
+    from unified_video_action_b200 import DiffActLoss, DiffLoss
+
+    kw = dict(n_frames=4, language_emb_model=None, language_emb_model_type=None, precision="fp32")
+    vid = DiffLoss(16, 768, 6, 1024, "100", **kw)
+    vid.net.load_state_dict({k: _T(v) for k, v in P.items()})
+    act = DiffActLoss(2, 768, 6, 1024, "100", **kw)
+    g0 = torch.Generator().manual_seed(11)
+    with torch.no_grad():
+        for prm in act.net.parameters():  # un-zero the zero-initialised tensors (DL:250-259)
+            if float(prm.abs().max()) == 0.0:
+                prm.copy_(0.02 * torch.randn(prm.shape, generator=g0))
+    vid, act = vid.to(dev), act.to(dev)
+    keys = set(act.state_dict().keys())
+    act.overlap_with(vid)
+    assert set(act.state_dict().keys()) == keys and not any(m is vid for m in act.modules())
+    assert isinstance(copy.deepcopy(act), DiffActLoss)
+    B = 2
+    gen = torch.Generator().manual_seed(5)
+    target = torch.randn(B, 1024, 16, generator=gen).to(dev)
+    mask = (torch.rand(B, 1024, generator=gen) > 0.2).float().to(dev)
+    actions = (torch.rand(B, 16, 2, generator=gen) * 2 - 1).to(dev)
+    z0 = torch.randn(B, 1024, 768, generator=gen).to(dev)
+
+    def run(flag):
+        monkeypatch.setenv("UVA_ACT_OVERLAP", flag)
+        for m in (vid, act):
+            for prm in m.parameters():
+                prm.grad = None
+        z = z0.clone().requires_grad_(True)
+        torch.manual_seed(99)
+        lv = vid(target, z, mask)
+        la = act(actions, z)
+        (lv + la).backward()
+        torch.cuda.synchronize()
+        return (float(lv), float(la), z.grad.clone(),
+                {k: prm.grad.clone() for m, tag in ((vid, "v."), (act, "a.")) for k, prm in ((tag + n, q) for n, q in m.named_parameters())})
+
+    lv0, la0, dz0, g_ser = run("0")
+    for _ in range(3):  # repeated: a missing stream dependency shows up as a flaky mismatch
+        lv1, la1, dz1, g_par = run("1")
+        assert lv1 == lv0 and la1 == la0
+        _check(dz1.cpu(), dz0.cpu(), 0, "dz")
+        assert g_par.keys() == g_ser.keys()
+        for k in g_ser:
+            _check(g_par[k].cpu(), g_ser[k].cpu(), 0, k)
+
+
 def test_error_paths(video):
     dev, _, P = video
     from unified_video_action_b200 import _lib

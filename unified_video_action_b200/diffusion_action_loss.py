@@ -8,10 +8,16 @@ the loss and the 100-step loop run in the CUDA library.
 """
 from __future__ import annotations
 
+import os
+import weakref
+from typing import Optional
+
 import torch
 import torch.nn as nn
 
-from .diffusion_loss import SimpleMLPAdaLN, _FusedLoss, _require_cuda, sample_rows
+from .diffusion_loss import _ENTRY, SimpleMLPAdaLN, _FusedLoss, _require_cuda, sample_rows
+
+_SIDE_STREAMS: dict = {}  # device index -> high-priority stream shared by the action heads of that device
 
 
 class DiffActLoss(nn.Module):
@@ -61,6 +67,7 @@ class DiffActLoss(nn.Module):
 
         self.num_timesteps = int(act_diff_training_steps)
         self.num_sampling_steps = int(act_diff_testing_steps)
+        object.__setattr__(self, "_fork_from", None)  # plain attribute: not a sub-module, not in state_dict
         self.net = SimpleMLPAdaLN(
             in_channels=target_channels, model_channels=width, out_channels=target_channels * 2,
             z_channels=z_channels, num_res_blocks=depth, grad_checkpointing=grad_checkpointing,
@@ -91,8 +98,62 @@ class DiffActLoss(nn.Module):
             return self.fc(z.transpose(1, 2)).transpose(1, 2)
         raise NotImplementedError
 
+    # ---- side-stream execution -------------------------------------------------------------
+    def overlap_with(self, other: Optional[nn.Module]) -> "DiffActLoss":
+        """Run this head beside ``other`` (the video ``DiffLoss`` that is called just before it with the
+        same ``z``, MAR:770-778): forward() then forks its side stream from the point where
+        ``other.forward`` was entered instead of from its own entry, so the 256-row action head and its
+        pre-net fill the gaps of the 16 384-row video head in the forward pass as well as in the backward
+        pass.  Requires that ``target`` of this head was complete on the stream before ``other`` was
+        called (true in MAR.forward_loss, where both are function arguments).  ``None`` undoes it."""
+        object.__setattr__(self, "_fork_from", None if other is None else weakref.ref(other))
+        if other is not None:
+            other._record_entry = True
+            quiet = getattr(torch.autograd.graph, "set_warn_on_accumulate_grad_stream_mismatch", None)
+            if quiet is not None:  # parameters are created on the default stream and used on the side stream on purpose
+                quiet(False)
+        return self
+
+    @staticmethod
+    def _side(dev) -> torch.cuda.Stream:
+        s = _SIDE_STREAMS.get(dev.index)
+        if s is None:
+            s = _SIDE_STREAMS[dev.index] = torch.cuda.Stream(device=dev, priority=-1)
+        return s
+
     def forward(self, target, z, task_mode=None, text_latents=None):
+        """DAL:109-166.  With autograd on (training) the pre-net, the fused loss and therefore (autograd
+        runs a backward node on the stream of its forward) their backward run on a high-priority side
+        stream: the head has 16 rows per sample, so alone it is a chain of ~150 launch-bound kernels; next
+        to the video head it costs nothing.  ``UVA_ACT_OVERLAP=0`` keeps everything on the caller's stream."""
         _require_cuda(z, "DiffActLoss.forward")
+        if not torch.is_grad_enabled() or os.environ.get("UVA_ACT_OVERLAP", "1") == "0":
+            return self._forward(target, z)
+        dev = z.device
+        cur = torch.cuda.current_stream(dev)
+        before = self.net._packed_key
+        with torch.cuda.device(dev):
+            self.net.head()  # a re-pack after an optimizer step stays on the caller's stream
+        ev = None
+        src = self._fork_from() if self._fork_from is not None else None
+        entry = _ENTRY.get(id(src)) if src is not None else None
+        if entry is not None and self.net._packed_key == before:
+            zref, ver, e = entry
+            if zref() is z and ver == z._version:  # the very tensor the video head was given, unmodified since
+                ev = e
+        if ev is None:
+            ev = cur.record_event()
+        side = self._side(dev)
+        side.wait_event(ev)
+        with torch.cuda.stream(side):
+            loss = self._forward(target, z)
+        z.record_stream(side)
+        target.record_stream(side)
+        cur.wait_stream(side)
+        loss.record_stream(cur)
+        return loss
+
+    def _forward(self, target, z):
         bsz, seq_len, _ = target.shape
         z = self.prenet(z)
         target = target.reshape(bsz * seq_len, -1)

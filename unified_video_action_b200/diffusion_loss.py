@@ -10,12 +10,18 @@ there is no PyTorch fallback.
 from __future__ import annotations
 
 import os
+import weakref
 from typing import List, Optional
 
 import torch
 import torch.nn as nn
 
 from . import _lib
+
+
+# id(DiffLoss module) -> (weak reference to z, z._version, event recorded when its forward() was entered);
+# kept outside the modules so that copy.deepcopy (EMA) and state_dict never see CUDA events
+_ENTRY: dict = {}
 
 
 def _mode_from(precision: Optional[str]) -> int:
@@ -223,9 +229,13 @@ class DiffLoss(nn.Module):
             precision=kwargs.get("precision"), T_train=self.num_timesteps, T_gen=int(num_sampling_steps),
         )
         self.num_sampling_steps = int(num_sampling_steps)
+        self._record_entry = False  # set by DiffActLoss.overlap_with(): remember where forward() was entered
 
     def forward(self, target, z, mask=None, conf_score=None, text_latents=None):
         _require_cuda(z, "DiffLoss.forward")
+        if self._record_entry:
+            # fork point for a head that runs beside this one on a side stream (see DiffActLoss.overlap_with)
+            _ENTRY[id(self)] = (weakref.ref(z), z._version, torch.cuda.current_stream(z.device).record_event())
         bsz, seq_len, _ = target.shape
         target = target.reshape(bsz * seq_len, -1)
         z = z.reshape(bsz * seq_len, -1)

@@ -44,6 +44,14 @@ def patch(mar_model: nn.Module, precision: Optional[str] = None) -> nn.Module:
         p = next(ref.parameters())
         new.to(device=p.device)
         setattr(mar_model, attr, new)
+    # the small heads run beside the video head on a side stream (MAR.forward_loss calls diffloss first
+    # with the same z, MAR:770-784)
+    vid = getattr(mar_model, "diffloss", None)
+    if isinstance(vid, DiffLoss):
+        for attr in ("diffactloss", "diffproploss"):
+            small = getattr(mar_model, attr, None)
+            if isinstance(small, DiffActLoss):
+                small.overlap_with(vid)
     return mar_model
 
 
