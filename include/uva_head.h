@@ -148,6 +148,23 @@ int uva_adamw_ema_step(int32_t n_tensors, float* const* params, const float* con
                        float* const* exp_avg, float* const* exp_avg_sq, float* const* ema,
                        const int64_t* numel, const float* weight_decay, const UvaAdamWHyper* hp, void* stream);
 
+/* The one collective of the path: data-parallel training all-reduces the head gradients.
+ * The reference leaves this to DDP's bucketed reducer under Accelerate
+ * (workspace/train_unified_video_action_workspace.py:290-292); here the fused backward writes every
+ * gradient of a head into ONE flat fp32 buffer, which is reduced in place with one ncclAllReduce on
+ * NVLink / NVSwitch (ncclAvg when average != 0, else ncclSum), enqueued on `stream` behind the backward.
+ * NCCL is bound at run time (the libnccl.so.2 already mapped into the process, else the system one); the
+ * calls fail with UVA_ERR_STATE when none can be loaded.  Sampling shards rows and needs no collective.
+ *   uva_nccl_unique_id  : rank 0 fills 128 bytes (host) that the caller broadcasts to the other ranks
+ *                         (any out-of-band channel: torch.distributed store, MPI, a file);
+ *   uva_nccl_comm_create: collective over all ranks; the current CUDA device is the rank's GPU;
+ *   uva_head_allreduce_grads: flat = device pointer to `count` fp32 values, reduced in place. */
+int32_t uva_nccl_version(void);
+int uva_nccl_unique_id(void* out128 /*host*/);
+int uva_nccl_comm_create(int32_t world_size, int32_t rank, const void* id128 /*host*/, void** comm /*host*/);
+int uva_nccl_comm_destroy(void* comm);
+int uva_head_allreduce_grads(void* comm, float* flat, int64_t count, int32_t average, void* stream);
+
 /* Number of kernel launches this handle has enqueued so far (bench.py's gpu_launches). */
 int64_t uva_head_launch_count(const UvaHead* h);
 

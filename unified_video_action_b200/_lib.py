@@ -73,7 +73,8 @@ SYMBOLS = [
     "uva_schedule_table", "uva_head_load_weights", "uva_head_workspace_bytes", "uva_head_net_forward",
     "uva_head_sample", "uva_head_loss_fwd", "uva_head_loss_bwd", "uva_head_launch_count",
     "uva_gemm_bf16_selftest", "uva_last_error", "uva_build_info", "uva_head_timing_enable", "uva_head_timing_read",
-    "uva_adamw_ema_step",
+    "uva_adamw_ema_step", "uva_nccl_version", "uva_nccl_unique_id", "uva_nccl_comm_create", "uva_nccl_comm_destroy",
+    "uva_head_allreduce_grads",
 ]
 
 
@@ -118,6 +119,16 @@ def lib() -> ctypes.CDLL:
         L.uva_head_timing_read.argtypes = [vp, i32, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(i64)]
         L.uva_adamw_ema_step.restype = ctypes.c_int
         L.uva_adamw_ema_step.argtypes = [i32, vp, vp, vp, vp, vp, vp, vp, vp, vp]
+        L.uva_nccl_version.restype = i32
+        L.uva_nccl_version.argtypes = []
+        L.uva_nccl_unique_id.restype = ctypes.c_int
+        L.uva_nccl_unique_id.argtypes = [vp]
+        L.uva_nccl_comm_create.restype = ctypes.c_int
+        L.uva_nccl_comm_create.argtypes = [i32, i32, vp, ctypes.POINTER(vp)]
+        L.uva_nccl_comm_destroy.restype = ctypes.c_int
+        L.uva_nccl_comm_destroy.argtypes = [vp]
+        L.uva_head_allreduce_grads.restype = ctypes.c_int
+        L.uva_head_allreduce_grads.argtypes = [vp, vp, i64, i32, vp]
         L.uva_last_error.restype = ctypes.c_char_p
         L.uva_build_info.restype = ctypes.c_char_p
         _lib = L
@@ -272,6 +283,45 @@ class Head:
                                        t.data_ptr(), noise.data_ptr(), N, dz.data_ptr(), arr, ws.data_ptr(),
                                        ws.numel(), _stream()), "uva_head_loss_bwd")
         return dz
+
+
+class GradComm:
+    """NCCL communicator of the head-gradient all-reduce, created through the C ABI.  The
+    128-byte unique id travels over the existing ``torch.distributed`` group (any backend); after that the
+    collective itself is ``uva_head_allreduce_grads`` on the caller's CUDA stream."""
+
+    def __init__(self, group=None):
+        import torch.distributed as dist
+
+        if not torch.cuda.is_available():
+            raise RuntimeError("GradComm needs a CUDA device (NCCL); there is no CPU path in the library")
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        buf = ctypes.create_string_buffer(128)
+        if self.rank == 0:
+            _check(lib().uva_nccl_unique_id(buf), "uva_nccl_unique_id")
+        box = [bytes(buf.raw)]
+        dist.broadcast_object_list(box, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+        c = ctypes.c_void_p()
+        _check(lib().uva_nccl_comm_create(self.world, self.rank, ctypes.create_string_buffer(box[0], 128), ctypes.byref(c)),
+               "uva_nccl_comm_create")
+        self._c = c
+        self.device = torch.device("cuda", torch.cuda.current_device())
+
+    def all_reduce_(self, flat: torch.Tensor, average: bool = True) -> torch.Tensor:
+        if not flat.is_cuda or flat.dtype != torch.float32 or not flat.is_contiguous():
+            raise RuntimeError("GradComm.all_reduce_: expected a contiguous fp32 CUDA tensor")
+        with torch.cuda.device(flat.device):
+            _check(lib().uva_head_allreduce_grads(self._c, flat.data_ptr(), flat.numel(), int(average), _stream()),
+                   "uva_head_allreduce_grads")
+        return flat
+
+    def __del__(self):
+        try:
+            if getattr(self, "_c", None):
+                lib().uva_nccl_comm_destroy(self._c)
+                self._c = None
+        except Exception:
+            pass
 
 
 def gemm_bf16_selftest(A: torch.Tensor, B: torch.Tensor, bias: Optional[torch.Tensor], block_n: int, layout: int = 0) -> torch.Tensor:

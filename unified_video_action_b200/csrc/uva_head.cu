@@ -455,3 +455,4 @@ extern "C" int uva_adamw_ema_step(int32_t n_tensors, float* const* params, const
 #include "head_small.inc"
 #include "head_sample.inc"
 #include "head_train.inc"
+#include "collective.inc"

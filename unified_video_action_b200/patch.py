@@ -83,10 +83,33 @@ def _shared_flat(grads):
     return torch.empty(0, dtype=g0.dtype, device=g0.device).set_(st, lo, (hi - lo,))
 
 
+_COMMS: dict = {}  # id(process group) -> _lib.GradComm (NCCL communicator created through the C ABI)
+
+
+def _reduce_flat(flat: torch.Tensor, group, average: bool, world: int) -> None:
+    """One in-place all-reduce of a flat fp32 buffer.  CUDA buffers go through the library
+    (``uva_head_allreduce_grads`` = ncclAllReduce with ncclAvg on the caller's stream); host buffers exist
+    only in the CPU tests of this host logic and use the torch.distributed group (gloo) directly."""
+    import torch.distributed as dist
+
+    if flat.is_cuda:
+        from . import _lib
+
+        key = (id(group), flat.device.index)
+        comm = _COMMS.get(key)
+        if comm is None:
+            comm = _COMMS[key] = _lib.GradComm(group)
+        comm.all_reduce_(flat, average)
+        return
+    dist.all_reduce(flat, group=group)
+    if average:
+        flat /= world
+
+
 def allreduce_head_grads(heads: Iterable[nn.Module], group=None, average: bool = True) -> int:
     """Data-parallel training: all-reduce of the head gradients over flat fp32 buffers (NCCL over NVLink
-    on GPUs, gloo in the CPU tests): one collective per flat gradient buffer of the fused backward plus
-    one for any other gradients of the head.  Returns the number of collectives issued."""
+    through the C ABI on GPUs, gloo in the CPU tests): one collective per flat gradient buffer of the fused
+    backward plus one for any other gradients of the head.  Returns the number of collectives issued."""
     import torch.distributed as dist
 
     n = 0
@@ -106,15 +129,11 @@ def allreduce_head_grads(heads: Iterable[nn.Module], group=None, average: bool =
             if flat is None:
                 loose.extend(members)
                 continue
-            dist.all_reduce(flat, group=group)
-            if average:
-                flat /= world
+            _reduce_flat(flat, group, average, world)
             n += 1
         if loose:
             flat = torch.cat([g.reshape(-1) for g in loose])
-            dist.all_reduce(flat, group=group)
-            if average:
-                flat /= world
+            _reduce_flat(flat, group, average, world)
             off = 0
             for g in loose:
                 g.copy_(flat[off:off + g.numel()].view_as(g))
