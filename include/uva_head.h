@@ -108,6 +108,17 @@ int uva_head_net_forward(UvaHead* h, const float* x, const int64_t* t, const flo
  *   teacher[j] before each step (per-step parity tests);
  *   trace (optional, may be NULL) [(k_end-k_begin),N,C]: receives the state after each step;
  *   runs loop iterations k_begin..k_end-1 (0..T_gen for the whole chain); out[N,C]. */
+/* step_noise may be NULL once uva_head_set_noise_seed(h, seed, offset, 1) has been called: the
+ * randn_like of GD:431 is then drawn inside the DDPM-update kernel from Philox4x32-10 keyed by `seed`,
+ * counter = (element index / 4, loop iteration k, offset), Box-Muller on 24-bit uniforms; the caller
+ * advances `offset` per sample() call.  Element index = row * C + c in the caller's [N, C] layout, so the
+ * samples do not depend on chunking.  This stream is NOT torch's randn stream: it is the mode for
+ * production sampling (no [T_gen, N, C] noise tensor in HBM); parity runs pass step_noise.
+ * uva_philox_normal writes the same numbers to memory: out[j * per_step + e] = draw e of step step0 + j. */
+int uva_head_set_noise_seed(UvaHead* h, uint64_t seed, uint32_t offset, int32_t enable);
+int uva_philox_normal(uint64_t seed, uint32_t offset, int32_t step0, int64_t per_step, int64_t n,
+                      float* out, void* stream);
+
 int uva_head_sample(UvaHead* h, const float* z, const float* x_init, const float* step_noise,
                     const float* teacher, float* trace, float temperature, float cfg_scale,
                     int32_t clip_denoised, int32_t k_begin, int32_t k_end, int64_t N, float* out,

@@ -544,3 +544,53 @@ def adamw_ema_step(params, grads, exp_avg, exp_avg_sq, ema, weight_decay, lr, be
         if ema is not None and ema[i] is not None:
             ema[i].mul_(ema_decay)
             ema[i].add_(p, alpha=1 - ema_decay)
+
+
+# ----------------------------------------------------------------------------------------------
+# Counter-based sampler noise ("step_noise NULL -> in-kernel Philox(seed, offset)").
+# Not a reference code path (the reference calls th.randn_like, GD:431): this restates the library's own
+# generator so that the kernel can be checked bit-for-bit on the integer part.  Philox4x32-10 is the
+# published algorithm (Salmon, Moraes, Dror, Shaw: "Parallel random numbers: as easy as 1, 2, 3", SC'11;
+# Random123 1.09), pinned below by the known-answer vectors of Random123's kat_vectors file.
+# ----------------------------------------------------------------------------------------------
+PHILOX_M0, PHILOX_M1 = 0xD2511F53, 0xCD9E8D57
+PHILOX_W0, PHILOX_W1 = 0x9E3779B9, 0xBB67AE85
+
+
+def philox4x32_10(c0, c1, c2, c3, k0, k1):
+    """Vectorised Philox4x32-10: uint32 arrays (broadcastable) -> four uint32 arrays."""
+    c = [np.asarray(v, dtype=np.uint64) & 0xFFFFFFFF for v in (c0, c1, c2, c3)]
+    k0 = np.uint64(k0 & 0xFFFFFFFF)
+    k1 = np.uint64(k1 & 0xFFFFFFFF)
+    mask = np.uint64(0xFFFFFFFF)
+    for _ in range(10):
+        p0 = np.uint64(PHILOX_M0) * c[0]
+        p1 = np.uint64(PHILOX_M1) * c[2]
+        hi0, lo0 = p0 >> np.uint64(32), p0 & mask
+        hi1, lo1 = p1 >> np.uint64(32), p1 & mask
+        c = [hi1 ^ c[1] ^ k0, lo1, hi0 ^ c[3] ^ k1, lo0]
+        k0 = (k0 + np.uint64(PHILOX_W0)) & mask
+        k1 = (k1 + np.uint64(PHILOX_W1)) & mask
+    return [v.astype(np.uint32) for v in c]
+
+
+def philox_normal(seed: int, offset: int, step0: int, per_step: int, steps: int) -> np.ndarray:
+    """[steps, per_step] float32 standard normals: element e of loop iteration k uses counter
+    (e >> 2 low, e >> 2 high, k, offset), key = seed; lanes (0,1) and (2,3) are Box-Muller pairs on 24-bit
+    uniforms u1 = ((a >> 8) + 1) / 2^24, u2 = (b >> 8) / 2^24 (elementwise.cuh: philox_normal)."""
+    e = np.arange(per_step, dtype=np.uint64)
+    blk = e >> np.uint64(2)
+    lane = (e & np.uint64(3)).astype(np.int64)
+    out = np.empty((steps, per_step), dtype=np.float32)
+    for j in range(steps):
+        r = philox4x32_10(blk & np.uint64(0xFFFFFFFF), blk >> np.uint64(32), np.uint64(step0 + j), np.uint64(offset),
+                          seed & 0xFFFFFFFF, (seed >> 32) & 0xFFFFFFFF)
+        r = np.stack(r, axis=0)  # [4, per_step]
+        a = np.take_along_axis(r, (lane & 2)[None, :], axis=0)[0]
+        b = np.take_along_axis(r, ((lane & 2) + 1)[None, :], axis=0)[0]
+        u1 = ((a >> np.uint32(8)).astype(np.float32) + np.float32(1.0)) * np.float32(1.0 / 16777216.0)
+        u2 = (b >> np.uint32(8)).astype(np.float32) * np.float32(1.0 / 16777216.0)
+        rad = np.sqrt(np.float32(-2.0) * np.log(u1.astype(np.float64))).astype(np.float32)
+        ang = 2.0 * np.pi * u2.astype(np.float64)
+        out[j] = rad * np.where(lane & 1, np.sin(ang), np.cos(ang)).astype(np.float32)
+    return out

@@ -376,6 +376,39 @@ def test_bf16_tracks_fp32_mode_at_baseline_rows(video, mode):
     _assert_close(a[sub][None], b[None], 1)
 
 
+def test_philox_noise_matches_oracle_and_materialised_run(video):
+    """step_noise == NULL: the DDPM-update kernel draws its noise from Philox4x32-10.
+    (i) the generator written to memory equals the numpy restatement (integer part bit-exact, so only the
+    float transform's last ulps differ), (ii) sampling with in-kernel noise equals sampling with the same
+    numbers passed as step_noise, bit for bit, on the chain path (N=16), the graph path (N=300), and the
+    chunked path with CFG (N=6000) — i.e. the draws do not depend on how rows are chunked."""
+    dev, g, P = video
+    from unified_video_action_b200 import _lib
+
+    seed, off = 0x1234567ABCDEF, 5
+    per, steps = 4099, 3
+    mine = _lib.philox_normal(seed, off, 7, per, steps, dev).cpu().numpy()
+    ref = O.philox_normal(seed, off, 7, per, steps)
+    assert np.abs(mine - ref).max() <= 2e-5
+    assert abs(float(mine.mean())) < 0.05 and abs(float(mine.std()) - 1) < 0.05
+    C = 16
+    h = _head(16, 768, 1024, 6, P, 1, dev)
+    gen = torch.Generator().manual_seed(21)
+    for N, cfg, k_end in ((16, 1.0, 100), (300, 1.0, 9), (6000, 3.0, 4)):
+        z = torch.randn(N, 768, generator=gen).to(dev)
+        x0 = torch.randn(N, C, generator=gen).to(dev)
+        if cfg != 1.0:
+            x0[N // 2:] = x0[:N // 2]
+        nz = _lib.philox_normal(seed, off, 0, N * C, k_end, dev).view(k_end, N, C)
+        a = h.sample(z, x0, nz, temperature=0.9, cfg=cfg, k_begin=0, k_end=k_end)
+        b = h.sample(z, x0, None, temperature=0.9, cfg=cfg, k_begin=0, k_end=k_end, seed=seed, offset=off)
+        torch.cuda.synchronize()
+        assert torch.equal(a, b), (N, float((a - b).abs().max()))
+        assert bool(torch.isfinite(a).all())
+    with pytest.raises(RuntimeError):
+        h.sample(z, x0, None, k_begin=0, k_end=2)  # neither noise nor seed
+
+
 def test_error_paths(video):
     dev, g, P = video
     from unified_video_action_b200 import _lib

@@ -154,3 +154,21 @@ def test_action_training_rows(golden_dir):
         terms = O.training_losses(P, S, _T(g["tr_target"]), _T(g["tr_t"]), _T(g["tr_noise"]), _T(g["tr_z"]))
     np.testing.assert_allclose(terms["loss"].numpy(), g["tr_rowloss"], rtol=1e-4, atol=1e-6)
     assert terms["loss"].mean().item() == pytest.approx(float(g["tr_loss"]), rel=1e-5)
+
+
+def test_philox_known_answers_and_moments():
+    """The sampler's optional in-kernel noise generator.  Philox4x32-10 is pinned by the
+    known-answer vectors published with Random123 (kat_vectors: "philox4x32 10 ..."), the normal transform
+    by its moments."""
+    def kat(c, k):
+        return [int(v) for v in O.philox4x32_10(*[np.uint64(x) for x in c], k[0], k[1])]
+
+    assert kat([0, 0, 0, 0], [0, 0]) == [0x6627E8D5, 0xE169C58D, 0xBC57AC4C, 0x9B00DBD8]
+    assert kat([0xFFFFFFFF] * 4, [0xFFFFFFFF] * 2) == [0x408F276D, 0x41C83B0E, 0xA20BC7C6, 0x6D5451FD]
+    assert kat([0x243F6A88, 0x85A308D3, 0x13198A2E, 0x03707344], [0xA4093822, 0x299F31D0]) == \
+        [0xD16CFE09, 0x94FDCCEB, 0x5001E420, 0x24126EA1]
+    x = O.philox_normal(seed=1234, offset=0, step0=0, per_step=1 << 18, steps=3)
+    assert abs(float(x.mean())) < 5e-3 and abs(float(x.std()) - 1.0) < 5e-3
+    assert abs(float(np.mean(x.astype(np.float64) ** 4)) - 3.0) < 0.1  # kurtosis of a normal
+    assert abs(float(np.corrcoef(x[0], x[1])[0, 1])) < 1e-2  # steps are independent streams
+    assert not np.array_equal(x[0], O.philox_normal(1234, 1, 0, 1 << 18, 1)[0])  # the call offset matters

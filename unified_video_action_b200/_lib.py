@@ -74,7 +74,7 @@ SYMBOLS = [
     "uva_head_sample", "uva_head_loss_fwd", "uva_head_loss_bwd", "uva_head_launch_count",
     "uva_gemm_bf16_selftest", "uva_last_error", "uva_build_info", "uva_head_timing_enable", "uva_head_timing_read",
     "uva_adamw_ema_step", "uva_nccl_version", "uva_nccl_unique_id", "uva_nccl_comm_create", "uva_nccl_comm_destroy",
-    "uva_head_allreduce_grads",
+    "uva_head_allreduce_grads", "uva_head_set_noise_seed", "uva_philox_normal",
 ]
 
 
@@ -119,6 +119,10 @@ def lib() -> ctypes.CDLL:
         L.uva_head_timing_read.argtypes = [vp, i32, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(i64)]
         L.uva_adamw_ema_step.restype = ctypes.c_int
         L.uva_adamw_ema_step.argtypes = [i32, vp, vp, vp, vp, vp, vp, vp, vp, vp]
+        L.uva_head_set_noise_seed.restype = ctypes.c_int
+        L.uva_head_set_noise_seed.argtypes = [vp, ctypes.c_uint64, ctypes.c_uint32, i32]
+        L.uva_philox_normal.restype = ctypes.c_int
+        L.uva_philox_normal.argtypes = [ctypes.c_uint64, ctypes.c_uint32, i32, i64, i64, vp, vp]
         L.uva_nccl_version.restype = i32
         L.uva_nccl_version.argtypes = []
         L.uva_nccl_unique_id.restype = ctypes.c_int
@@ -235,20 +239,28 @@ class Head:
         return out
 
     def sample(self, z, x_init, step_noise, temperature=1.0, cfg=1.0, clip_denoised=False, teacher=None,
-               trace=False, k_begin=0, k_end=None):
+               trace=False, k_begin=0, k_end=None, seed=None, offset=0):
+        """``step_noise`` [steps, N, C], or ``None`` with ``seed`` (and a per-call ``offset``): the noise is
+        then drawn in the kernel from Philox4x32-10 (no noise tensor in HBM)."""
         z, x_init = _f32c(z, "z"), _f32c(x_init, "x_init")
         N = z.shape[0]
         k_end = self.T_gen if k_end is None else k_end
-        step_noise = _f32c(step_noise, "step_noise")
-        if step_noise.shape[0] < k_end - k_begin or step_noise.shape[1:] != x_init.shape:
-            raise RuntimeError("step_noise must be [k_end-k_begin, N, C]")
+        if step_noise is None:
+            if seed is None:
+                raise RuntimeError("sample: pass step_noise or a seed for the in-kernel Philox generator")
+            _check(lib().uva_head_set_noise_seed(self._h, int(seed) & (2**64 - 1), int(offset) & 0xFFFFFFFF, 1),
+                   "uva_head_set_noise_seed")
+        else:
+            step_noise = _f32c(step_noise, "step_noise")
+            if step_noise.shape[0] < k_end - k_begin or step_noise.shape[1:] != x_init.shape:
+                raise RuntimeError("step_noise must be [k_end-k_begin, N, C]")
         teacher = None if teacher is None else _f32c(teacher, "teacher")
         tr = torch.empty(k_end - k_begin, N, self.C, dtype=torch.float32, device=z.device) if trace else None
         out = torch.empty(N, self.C, dtype=torch.float32, device=z.device)
         if N == 0:
             return (out, tr) if trace else out
         ws = self.workspace(N, 0)
-        _check(lib().uva_head_sample(self._h, z.data_ptr(), x_init.data_ptr(), step_noise.data_ptr(), _ptr(teacher),
+        _check(lib().uva_head_sample(self._h, z.data_ptr(), x_init.data_ptr(), _ptr(step_noise), _ptr(teacher),
                                      _ptr(tr), float(temperature), float(cfg), int(bool(clip_denoised)), int(k_begin),
                                      int(k_end), N, out.data_ptr(), ws.data_ptr(), ws.numel(), _stream()),
                "uva_head_sample")
@@ -283,6 +295,15 @@ class Head:
                                        t.data_ptr(), noise.data_ptr(), N, dz.data_ptr(), arr, ws.data_ptr(),
                                        ws.numel(), _stream()), "uva_head_loss_bwd")
         return dz
+
+
+def philox_normal(seed: int, offset: int, step0: int, per_step: int, steps: int, device) -> torch.Tensor:
+    """[steps, per_step] standard normals of the sampler's in-kernel generator, written to memory."""
+    out = torch.empty(steps, per_step, dtype=torch.float32, device=device)
+    with torch.cuda.device(out.device):
+        _check(lib().uva_philox_normal(int(seed) & (2**64 - 1), int(offset) & 0xFFFFFFFF, int(step0), int(per_step),
+                                       out.numel(), out.data_ptr(), _stream()), "uva_philox_normal")
+    return out
 
 
 class GradComm:

@@ -312,10 +312,57 @@ struct StepCoef {
   int nonzero;
 };
 
+// Counter-based noise for the sampler when the caller passes no step_noise ("NULL ->
+// in-kernel Philox(seed, offset)"): Philox4x32-10 (Salmon et al., SC'11; the generator behind
+// torch.randn on CUDA) keyed by the 64-bit seed, counter = (element index / 4, loop iteration k, call
+// offset), two Box-Muller pairs per block.  The value of element e of step k depends on nothing else, so
+// row chunking, the two-lane overlap and multi-GPU row sharding (with global row indices) do not change
+// the samples.  oracle.philox_normal restates it in numpy.
+struct PhiloxSeed {
+  uint32_t k0, k1;  // seed low / high
+  uint32_t offset;  // per-call counter word
+  uint32_t on;      // 0: noise comes from memory
+};
+
+__device__ __forceinline__ void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0,
+                                              uint32_t k1, uint32_t out[4]) {
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    const uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+    const uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+    c0 = hi1 ^ c1 ^ k0; c1 = lo1; c2 = hi0 ^ c3 ^ k1; c3 = lo0;
+    k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+  }
+  out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+}
+
+// standard normal number `e` of loop iteration `step`
+__device__ __forceinline__ float philox_normal(const PhiloxSeed& s, uint32_t step, uint64_t e) {
+  uint32_t r[4];
+  const uint64_t blk = e >> 2;
+  philox4x32_10((uint32_t)blk, (uint32_t)(blk >> 32), step, s.offset, s.k0, s.k1, r);
+  const int lane = (int)(e & 3);
+  const uint32_t a = r[lane & 2], b = r[(lane & 2) + 1];
+  const float u1 = ((float)(a >> 8) + 1.0f) * (1.0f / 16777216.0f);  // (0, 1]
+  const float u2 = (float)(b >> 8) * (1.0f / 16777216.0f);           // [0, 1)
+  const float rad = sqrtf(-2.0f * logf(u1));
+  float sn, cs;
+  sincospif(2.0f * u2, &sn, &cs);
+  return rad * ((lane & 1) ? sn : cs);
+}
+
+__global__ void k_philox_fill(PhiloxSeed s, uint32_t step0, int64_t per_step, int64_t n, float* __restrict__ out) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t j = i / per_step;
+    out[i] = philox_normal(s, step0 + (uint32_t)j, (uint64_t)(i - j * per_step));
+  }
+}
+
 __global__ void k_ddpm_step(const float* __restrict__ net, int ldn, const float* __restrict__ x_cur,
                             const float* __restrict__ noise, float* __restrict__ x_next, int64_t rows,
                             int C, int64_t half, int64_t g0, int64_t ghalf, float cfg,
-                            float temperature, int clip, StepCoef k) {
+                            float temperature, int clip, StepCoef k, PhiloxSeed ps = PhiloxSeed{0, 0, 0, 0},
+                            uint32_t step = 0) {
   const int64_t n = rows * C;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
        i += (int64_t)gridDim.x * blockDim.x) {
@@ -341,7 +388,8 @@ __global__ void k_ddpm_step(const float* __restrict__ net, int ldn, const float*
     if (k.nonzero) {
       // noise lives in the caller's [N, C] layout: chunk-local row r -> global row
       const int64_t gr = g0 + ((half > 0 && r >= half) ? ghalf + (r - half) : r);
-      out = mean + expf(0.5f * logvar) * noise[gr * C + c] * temperature;
+      const float nz = ps.on ? philox_normal(ps, step, (uint64_t)(gr * C + c)) : noise[gr * C + c];
+      out = mean + expf(0.5f * logvar) * nz * temperature;
     }
     x_next[i] = out;
   }

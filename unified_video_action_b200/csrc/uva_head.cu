@@ -175,6 +175,7 @@ struct UvaHead {
   bool quad = false;  // UVA_QUAD: clusters of two CTA pairs with multicast A boxes (forward-form GEMMs)
   bool fuse_ln = true;  // UVA_FUSE_LN: LayerNorm-modulate inside the AdaLN GEMM epilogue (bf16 sampling path)
   int grid_mult = 1;  // UVA_GRID_MULT: GEMM grids of grid_mult x #SMs CTAs (block scheduler balances the tail)
+  PhiloxSeed noise{0, 0, 0, 0};  // uva_head_set_noise_seed: generator of the sampler's noise when step_noise == NULL
   int dbg_skip = 0;  // UVA_DEBUG_SKIP (timing diagnosis only, results are wrong): 1 = no GEMM launches, 2 = no row kernels
   // latency path (head_small.inc): small batches run with the AdaLN modulation of all denoise steps
   // computed up front and the whole chain replayed from a CUDA graph
@@ -215,6 +216,26 @@ static inline int grid_for(int64_t n, int threads, int sms) {
 }
 
 extern "C" int64_t uva_head_launch_count(const UvaHead* h) { return h ? h->launches : 0; }
+
+extern "C" int uva_head_set_noise_seed(UvaHead* h, uint64_t seed, uint32_t offset, int32_t enable) {
+  if (!h) return fail(UVA_ERR_INVALID, "set_noise_seed: null handle");
+  h->noise = PhiloxSeed{(uint32_t)seed, (uint32_t)(seed >> 32), offset, enable ? 1u : 0u};
+  return UVA_OK;
+}
+
+extern "C" int uva_philox_normal(uint64_t seed, uint32_t offset, int32_t step0, int64_t per_step, int64_t n, float* out,
+                                 void* stream) {
+  if (!out || n < 0 || per_step <= 0 || step0 < 0) return fail(UVA_ERR_INVALID, "philox_normal: bad argument");
+  if (n == 0) return UVA_OK;
+  int dev = 0, sms = 0;
+  CUDA_TRY(cudaGetDevice(&dev));
+  CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  const PhiloxSeed s{(uint32_t)seed, (uint32_t)(seed >> 32), offset, 1u};
+  k_philox_fill<<<grid_for(n, 256, sms), 256, 0, (cudaStream_t)stream>>>(s, (uint32_t)step0, per_step, n, out);
+  const cudaError_t e = cudaPeekAtLastError();
+  if (e != cudaSuccess) return fail(UVA_ERR_CUDA, "philox_normal: %s", cudaGetErrorString(e));
+  return UVA_OK;
+}
 
 extern "C" int uva_head_timing_enable(UvaHead* h, int32_t enable) {
   if (!h) return fail(UVA_ERR_INVALID, "timing_enable: null handle");

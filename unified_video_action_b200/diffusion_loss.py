@@ -117,6 +117,7 @@ class SimpleMLPAdaLN(nn.Module):
         self._head: Optional[_lib.Head] = None
         self._packed_key = None
         self._names = param_names(num_res_blocks)
+        self.device_noise: Optional[bool] = None  # True: in-kernel Philox step noise (default: UVA_B200_NOISE env, "torch")
 
     def initialize_weights(self):
         """Same scheme as DL:237-259: Xavier-uniform Linears with zero bias, N(0, 0.02) timestep MLP,
@@ -263,6 +264,13 @@ def sample_rows(net: SimpleMLPAdaLN, z, C: int, steps: int, temperature: float, 
         noise = torch.cat([noise, noise], dim=0)
     else:
         noise = torch.randn(N, C).to(dev)
+    if (getattr(net, "device_noise", None) if getattr(net, "device_noise", None) is not None
+            else os.environ.get("UVA_B200_NOISE", "torch") == "philox"):
+        # production mode: per-step noise drawn inside the DDPM-update kernel (Philox4x32-10), no
+        # [steps, N, C] tensor; the seed comes from torch's CPU generator so manual_seed still reproduces it
+        seed = int(torch.randint(0, 2**62, (1,)).item())
+        with torch.cuda.device(dev):
+            return net.head().sample(z, noise, None, temperature=temperature, cfg=cfg, clip_denoised=clip_denoised, seed=seed)
     # one CUDA randn per step, as th.randn_like(x) inside p_sample (GD:431)
     step_noise = torch.empty(steps, N, C, dtype=torch.float32, device=dev)
     for k in range(steps):
