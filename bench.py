@@ -188,6 +188,20 @@ def measure_latency(dev, batches=(1, 56), calls=200):
         out[f"B{B}_rows{16 * B}"] = {"p50_ms": ts[len(ts) // 2], "p90_ms": ts[int(len(ts) * 0.9)], "calls": calls,
                                     "row_steps_per_s": 16 * B * T_GEN / (ts[len(ts) // 2] / 1e3),
                                     "launches_per_call": launches}
+        # production mode: step noise drawn in the kernel (Philox4x32-10) instead of 100 torch.randn calls that
+        # keep the reference's RNG stream
+        head.net.device_noise = True
+        for _ in range(5):
+            head.sample(z, temperature=TEMP, cfg=1.0).cpu()
+        ts = []
+        for _ in range(calls):
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            head.sample(z, temperature=TEMP, cfg=1.0).cpu()
+            ts.append((time.perf_counter() - t0) * 1e3)
+        head.net.device_noise = None
+        ts.sort()
+        out[f"B{B}_rows{16 * B}"]["p50_ms_device_noise"] = ts[len(ts) // 2]
     return out
 
 
