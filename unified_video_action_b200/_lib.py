@@ -85,7 +85,7 @@ def lib() -> ctypes.CDLL:
             return _lib
         if needs_build():
             build()
-        L = ctypes.CDLL(LIB_PATH)
+        L = ctypes.CDLL(os.environ.get("UVA_HEAD_LIB") or LIB_PATH)  # UVA_HEAD_LIB: an experimental build of the same sources
         vp, i32, i64, f32 = ctypes.c_void_p, ctypes.c_int32, ctypes.c_int64, ctypes.c_float
         L.uva_head_num_params.restype = i32
         L.uva_head_num_params.argtypes = [i32]

@@ -22,6 +22,14 @@ __device__ __forceinline__ float silu_tanh(float x) {
   asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(hx));
   return fmaf(hx, t, hx);
 }
+// derivative of SiLU through one MUFU op (bf16 GEMM epilogues: the operand x is a bf16 pre-activation, whose
+// rounding error is 4x the 2^-11 of tanh.approx): s = sigmoid(x) = 0.5 + 0.5 tanh(0.5 x); s + x s (1 - s)
+__device__ __forceinline__ float dsilu_tanh(float x) {
+  float t;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(0.5f * x));
+  const float s = fmaf(0.5f, t, 0.5f);
+  return s * fmaf(x, 1.0f - s, 1.0f);
+}
 // derivative of SiLU given x: s + x*s*(1-s), s = sigmoid(x)
 __device__ __forceinline__ float dsilu_f(float x) {
   float s = 1.0f / (1.0f + __expf(-x));
@@ -146,7 +154,11 @@ __device__ __forceinline__ void tma_store_2d(const CUtensorMap* m, const void* s
 }
 __device__ __forceinline__ void bulk_commit_group() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 // all bulk groups of this thread have finished READING their shared-memory source
+#ifdef UVA_EXP_NO_STORE_WAIT  // timing experiment only (results may be wrong): upper bound of what decoupling the store wait buys
+__device__ __forceinline__ void bulk_wait_read_all() {}
+#else
 __device__ __forceinline__ void bulk_wait_read_all() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+#endif
 // all bulk groups of this thread are complete (writes visible)
 __device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 // named barrier among `threads` threads (whole warps) of the CTA
