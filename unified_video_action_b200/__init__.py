@@ -9,5 +9,7 @@ from .diffusion_loss import DiffLoss, SimpleMLPAdaLN, param_names  # noqa: F401
 from .diffusion_action_loss import DiffActLoss  # noqa: F401
 from .patch import patch, shard_rows, allreduce_head_grads  # noqa: F401
 from .optim import HeadAdamW, ema_decay_at  # noqa: F401
+from .checkpoint import export_head_state_dict, head_state_dicts, load_reference_checkpoint  # noqa: F401
 
-__all__ = ["DiffLoss", "DiffActLoss", "SimpleMLPAdaLN", "param_names", "patch", "shard_rows", "allreduce_head_grads", "HeadAdamW", "ema_decay_at"]
+__all__ = ["DiffLoss", "DiffActLoss", "SimpleMLPAdaLN", "param_names", "patch", "shard_rows", "allreduce_head_grads", "HeadAdamW", "ema_decay_at",
+           "load_reference_checkpoint", "head_state_dicts", "export_head_state_dict"]
