@@ -409,6 +409,29 @@ def test_philox_noise_matches_oracle_and_materialised_run(video):
         h.sample(z, x0, None, k_begin=0, k_end=2)  # neither noise nor seed
 
 
+def test_chain_kernel_cluster_staging_equals_plain_grid(video, monkeypatch):
+    """predict_action regime (N <= 32): the persistent chain kernel with clusters of 4 CTAs sharing the
+    activation staging through distributed shared memory must give the very bits of the plain cooperative
+    grid (same arithmetic, only who loads which row differs), for one and two 16-row tiles, with and
+    without CFG."""
+    dev, g, P = video
+    h = _head(16, 768, 1024, 6, P, 1, dev)
+    gen = torch.Generator().manual_seed(33)
+    for N, cfg, clip, k_end in ((16, 1.0, True, 100), (27, 1.0, False, 40), (32, 3.0, False, 25), (5, 1.0, True, 100)):
+        z = torch.randn(N, 768, generator=gen).to(dev)
+        x0 = torch.randn(N, 16, generator=gen).to(dev)
+        if cfg != 1.0:
+            x0[N // 2:] = x0[:N // 2]
+        nz = torch.randn(k_end, N, 16, generator=gen).to(dev)
+        outs = {}
+        for cl in ("1", "4"):
+            monkeypatch.setenv("UVA_CHAIN_CL", cl)
+            outs[cl] = h.sample(z, x0, nz, temperature=0.95, cfg=cfg, clip_denoised=clip, k_begin=0, k_end=k_end)
+            torch.cuda.synchronize()
+        assert bool(torch.isfinite(outs["4"]).all())
+        assert torch.equal(outs["1"], outs["4"]), (N, float((outs["1"] - outs["4"]).abs().max()))
+
+
 def test_error_paths(video):
     dev, g, P = video
     from unified_video_action_b200 import _lib

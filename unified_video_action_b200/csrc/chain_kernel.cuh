@@ -62,6 +62,7 @@ struct ChainArgs {
   int half;            // N / 2 with CFG, else 0
   float cfg, temperature;
   int clip;
+  int dbg;  // UVA_CHAIN_DBG (timing diagnosis only, results are wrong): 1 = no grid barriers, 2 = no activation staging
 };
 
 __device__ __forceinline__ void mma_bf16_16816(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3,
@@ -73,7 +74,8 @@ __device__ __forceinline__ void mma_bf16_16816(float (&c)[4], uint32_t a0, uint3
 }
 
 // grid-wide barrier: every CTA arrives once per epoch on a monotonically increasing counter
-__device__ __forceinline__ void chain_grid_sync(unsigned int* counter, unsigned int& epoch) {
+__device__ __forceinline__ void chain_grid_sync(unsigned int* counter, unsigned int& epoch, int dbg = 0) {
+  if (dbg & 1) { __syncthreads(); return; }
   __syncthreads();
   if (threadIdx.x == 0) {
     epoch += 1;
@@ -204,6 +206,109 @@ __device__ __forceinline__ void ch_stage_b16(uint32_t* A, const bf16* src, int m
   }
 }
 
+// ---- cluster-cooperative staging (CL CTAs of a cluster share the work of staging one activation tile) ----
+// Every CTA needs the whole 16-row tile, so without clusters each of the 128 CTAs pulls all of it from L2
+// (8 MB of L2 reads per layer) and normalises all 16 rows.  In a cluster of CL CTAs, CTA `rank` loads and
+// normalises only rows [rank * 16/CL, (rank+1) * 16/CL) and writes the bf16 result into the tile of every CTA of
+// the cluster through distributed shared memory; a cluster barrier then publishes the tile.
+__device__ __forceinline__ uint32_t ch_mapa(uint32_t local_addr, uint32_t cta) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local_addr), "r"(cta));
+  return r;
+}
+__device__ __forceinline__ void ch_st_cluster_v2(uint32_t addr, uint32_t x, uint32_t y) {
+  asm volatile("st.shared::cluster.v2.u32 [%0], {%1, %2};" ::"r"(addr), "r"(x), "r"(y) : "memory");
+}
+__device__ __forceinline__ void ch_st_cluster_v4(uint32_t addr, uint4 v) {
+  asm volatile("st.shared::cluster.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+// same arithmetic as ch_stage_lnmod (bit-identical tile), one warp per row, rows of this CTA only
+template <int CL>
+__device__ __forceinline__ void ch_stage_lnmod_cl(uint32_t* A, const float* h, int m0, int N, const float* ln_w,
+                                                  const float* ln_b, const bf16* shift, const bf16* scale,
+                                                  int64_t ldmod, int warp, int lane, uint32_t rank) {
+  constexpr int RPC = CH_MT / CL;  // rows per CTA
+  if (warp >= RPC) return;
+  const int rl = (int)rank * RPC + warp;
+  const int row = m0 + rl;
+  const int sw = (rl & 7) << 2;
+  uint32_t dst[CL];
+  const uint32_t local = smem_u32(A + rl * (CH_W / 2));
+#pragma unroll
+  for (int c = 0; c < CL; ++c) dst[c] = ch_mapa(local, (uint32_t)c);
+  if (row >= N) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+#pragma unroll
+      for (int c = 0; c < CL; ++c) ch_st_cluster_v2(dst[c] + 4u * (uint32_t)((2 * (i * 32 + lane)) ^ sw), 0u, 0u);
+    }
+    return;
+  }
+  const float4* hp = reinterpret_cast<const float4*>(h + (int64_t)row * CH_W);
+  const uint2* shp = reinterpret_cast<const uint2*>(shift + (int64_t)row * ldmod);
+  const uint2* scp = reinterpret_cast<const uint2*>(scale + (int64_t)row * ldmod);
+  float4 v[8];
+  uint2 shv[8], scv[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) v[i] = __ldcg(hp + i * 32 + lane);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    shv[i] = __ldg(shp + i * 32 + lane);
+    scv[i] = __ldg(scp + i * 32 + lane);
+  }
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) s += (v[i].x + v[i].y) + (v[i].z + v[i].w);
+  const float mean = warp_sum(s) * (1.0f / CH_W);
+  float q = 0.f;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const float a = v[i].x - mean, b = v[i].y - mean, c = v[i].z - mean, d = v[i].w - mean;
+    q += (a * a + b * b) + (c * c + d * d);
+  }
+  const float rstd = rsqrtf(warp_sum(q) * (1.0f / CH_W) + 1e-6f);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int e = i * 32 + lane;
+    float n0 = (v[i].x - mean) * rstd, n1 = (v[i].y - mean) * rstd, n2 = (v[i].z - mean) * rstd, n3 = (v[i].w - mean) * rstd;
+    if (ln_w != nullptr) {
+      const float4 gw = __ldg(reinterpret_cast<const float4*>(ln_w) + e);
+      const float4 gb = __ldg(reinterpret_cast<const float4*>(ln_b) + e);
+      n0 = fmaf(n0, gw.x, gb.x); n1 = fmaf(n1, gw.y, gb.y); n2 = fmaf(n2, gw.z, gb.z); n3 = fmaf(n3, gw.w, gb.w);
+    }
+    const uint2 sh = shv[i], sc = scv[i];
+    const float2 sh01 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&sh.x));
+    const float2 sh23 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&sh.y));
+    const float2 sc01 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&sc.x));
+    const float2 sc23 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&sc.y));
+    const uint32_t p0 = pack_bf16x2(fmaf(n0, 1.0f + sc01.x, sh01.x), fmaf(n1, 1.0f + sc01.y, sh01.y));
+    const uint32_t p1 = pack_bf16x2(fmaf(n2, 1.0f + sc23.x, sh23.x), fmaf(n3, 1.0f + sc23.y, sh23.y));
+    const uint32_t off = 4u * (uint32_t)((2 * e) ^ sw);
+#pragma unroll
+    for (int c = 0; c < CL; ++c) ch_st_cluster_v2(dst[c] + off, p0, p1);
+  }
+}
+
+// rows of this CTA of a bf16 [N, W] activation -> the tile of every CTA of the cluster
+template <int CL>
+__device__ __forceinline__ void ch_stage_b16_cl(uint32_t* A, const bf16* src, int m0, int N, int tid, uint32_t rank) {
+  constexpr int RPC = CH_MT / CL;
+  const uint32_t base = smem_u32(A);
+#pragma unroll
+  for (int i = 0; i < (RPC * (CH_W / 8) + CH_THREADS - 1) / CH_THREADS; ++i) {
+    const int qd = i * CH_THREADS + tid;
+    if (qd >= RPC * (CH_W / 8)) break;
+    const int rl = (int)rank * RPC + (qd >> 7), c = qd & 127;
+    uint4 v = make_uint4(0u, 0u, 0u, 0u);
+    if (m0 + rl < N) v = __ldcg(reinterpret_cast<const uint4*>(src + (int64_t)(m0 + rl) * CH_W) + c);
+    const uint32_t off = 4u * (uint32_t)(rl * (CH_W / 2) + ((c ^ (rl & 7)) << 2));
+#pragma unroll
+    for (int d = 0; d < CL; ++d) ch_st_cluster_v4(ch_mapa(base + off, (uint32_t)d), v);
+  }
+}
+
+template <int CL>
 __global__ void __launch_bounds__(CH_THREADS, 1) k_denoise_chain(const __grid_constant__ ChainArgs p) {
   extern __shared__ __align__(16) uint8_t ch_smem[];
   uint32_t* Wsm = reinterpret_cast<uint32_t*>(ch_smem);              // [2*depth][8][512 words]
@@ -215,6 +320,7 @@ __global__ void __launch_bounds__(CH_THREADS, 1) k_denoise_chain(const __grid_co
   const int N = p.N, C = p.C, W = CH_W;
   const int mtiles = (N + CH_MT - 1) / CH_MT;
   unsigned int epoch = 0;
+  const uint32_t crank = (CL > 1) ? cluster_ctarank() : 0u;
 
   // stationary weights: this CTA's 8 rows of every MLP matrix
   for (int l = 0; l < 2 * p.depth; ++l) {
@@ -277,7 +383,7 @@ __global__ void __launch_bounds__(CH_THREADS, 1) k_denoise_chain(const __grid_co
         for (int c = 0; c < C; ++c) acc = fmaf(xs[rs * C + c], __ldg(wi + c), acc);
         p.h[(int64_t)r * W + f0 + n] = acc;
       }
-      chain_grid_sync(p.counter, epoch);
+      chain_grid_sync(p.counter, epoch, p.dbg);
     }
     const bf16* modj = p.mod + (int64_t)j * N * p.nmod;
     for (int b = 0; b < p.depth; ++b) {
@@ -285,8 +391,13 @@ __global__ void __launch_bounds__(CH_THREADS, 1) k_denoise_chain(const __grid_co
       // ---- GEMM1: u = SiLU(LNmod(h) . W1^T + b1) (DL:163-166) ----
       for (int mt = 0; mt < mtiles; ++mt) {
         const int m0 = mt * CH_MT;
-        ch_stage_lnmod(A, p.h, m0, N, p.ln_w[b], p.ln_b[b], shift, shift + W, p.nmod, warp, lane);
-        __syncthreads();
+        if constexpr (CL > 1) {
+          if (!(p.dbg & 2)) ch_stage_lnmod_cl<CL>(A, p.h, m0, N, p.ln_w[b], p.ln_b[b], shift, shift + W, p.nmod, warp, lane, crank);
+          cluster_sync_all();  // every CTA of the cluster has written its rows into this CTA's tile
+        } else {
+          if (!(p.dbg & 2)) ch_stage_lnmod(A, p.h, m0, N, p.ln_w[b], p.ln_b[b], shift, shift + W, p.nmod, warp, lane);
+          __syncthreads();
+        }
         ch_gemm_patch(A, Wsm + (2 * b) * (CH_F * (W / 2)), red, warp, lane);
         if (tid < CH_MT * CH_F) {
           const int rl = tid >> 3, n = tid & 7;
@@ -295,14 +406,20 @@ __global__ void __launch_bounds__(CH_THREADS, 1) k_denoise_chain(const __grid_co
             p.u[(int64_t)(m0 + rl) * W + f0 + n] = __float2bfloat16_rn(silu_f(v));
           }
         }
-        __syncthreads();
+        // the tile doubles as the reduction scratch: peers may only overwrite it once this CTA is done with it
+        if (CL > 1 && mt + 1 < mtiles) cluster_sync_all(); else __syncthreads();
       }
-      chain_grid_sync(p.counter, epoch);
+      chain_grid_sync(p.counter, epoch, p.dbg);
       // ---- GEMM2: h += gate * (u . W2^T + b2) (DL:167) ----
       for (int mt = 0; mt < mtiles; ++mt) {
         const int m0 = mt * CH_MT;
-        ch_stage_b16(A, p.u, m0, N, tid);
-        __syncthreads();
+        if constexpr (CL > 1) {
+          if (!(p.dbg & 2)) ch_stage_b16_cl<CL>(A, p.u, m0, N, tid, crank);
+          cluster_sync_all();
+        } else {
+          if (!(p.dbg & 2)) ch_stage_b16(A, p.u, m0, N, tid);
+          __syncthreads();
+        }
         ch_gemm_patch(A, Wsm + (2 * b + 1) * (CH_F * (W / 2)), red, warp, lane);
         if (tid < CH_MT * CH_F) {
           const int rl = tid >> 3, n = tid & 7;
@@ -313,9 +430,9 @@ __global__ void __launch_bounds__(CH_THREADS, 1) k_denoise_chain(const __grid_co
             *hp = fmaf(gate, v, __ldcg(hp));
           }
         }
-        __syncthreads();
+        if (CL > 1 && mt + 1 < mtiles) cluster_sync_all(); else __syncthreads();
       }
-      chain_grid_sync(p.counter, epoch);
+      chain_grid_sync(p.counter, epoch, p.dbg);
     }
     // ---- final layer (DL:185-189): CTA o < 2C computes output column o ----
     if ((int)blockIdx.x < 2 * C) {
@@ -347,7 +464,7 @@ __global__ void __launch_bounds__(CH_THREADS, 1) k_denoise_chain(const __grid_co
         __syncwarp();
       }
     }
-    chain_grid_sync(p.counter, epoch);
+    chain_grid_sync(p.counter, epoch, p.dbg);
   }
 }
 
