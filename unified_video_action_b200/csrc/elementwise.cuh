@@ -38,6 +38,65 @@ __global__ void k_pack_ada_perm(const float* __restrict__ src, const float* __re
   }
 }
 
+// One launch re-packs every parameter of a head (uva_head_load_weights): tensor t = blockIdx.y is read once and
+// written as (a) the fp32 copy in the handle's own layout, (b) its bf16 GEMM operand (Linear weights, bf16 mode),
+// (c) for the AdaLN modulation Linears the bf16 copy in (shift | scale)-tile row order of k_pack_ada_perm, resp.
+// the fp32 bias in the same order.  Replaces ~50 device-to-device copies + ~25 pack launches per call.
+constexpr int LOAD_MAX_JOBS = 40;
+struct LoadJob {
+  const float* src;
+  float* dst32;
+  bf16* dst16;    // may be null
+  bf16* perm16;   // may be null: weight rows permuted (element i = row * cols + k)
+  float* perm32;  // may be null: bias permuted (element i = row)
+  int64_t n;
+  int cols;       // row length for perm16 (ignored otherwise)
+  int W;          // model width: rows [0, W) shift, [W, 2W) scale, rest unchanged
+};
+struct LoadBatch {
+  LoadJob job[LOAD_MAX_JOBS];
+  int count;
+};
+__device__ __forceinline__ int ada_perm_row(int sr, int W) {
+  if (sr < W) return (sr >> 7) * 256 + (sr & 127);
+  if (sr < 2 * W) return ((sr - W) >> 7) * 256 + 128 + ((sr - W) & 127);
+  return sr;
+}
+__global__ void __launch_bounds__(256) k_load_params(const __grid_constant__ LoadBatch b) {
+  if ((int)blockIdx.y >= b.count) return;
+  const LoadJob& j = b.job[blockIdx.y];
+  const bool vec = ((reinterpret_cast<uintptr_t>(j.src) | reinterpret_cast<uintptr_t>(j.dst32) | reinterpret_cast<uintptr_t>(j.dst16) |
+                     reinterpret_cast<uintptr_t>(j.perm16)) & 15) == 0 && (j.cols % 4 == 0 || j.perm16 == nullptr);
+  const int64_t n4 = vec ? j.n / 4 : 0;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+    const float4 v = reinterpret_cast<const float4*>(j.src)[i];
+    reinterpret_cast<float4*>(j.dst32)[i] = v;
+    const uint2 pk = make_uint2(pack_bf16x2(v.x, v.y), pack_bf16x2(v.z, v.w));
+    if (j.dst16) reinterpret_cast<uint2*>(j.dst16)[i] = pk;
+    if (j.perm16) {
+      const int64_t e = 4 * i;
+      const int sr = (int)(e / j.cols);
+      const int k = (int)(e - (int64_t)sr * j.cols);
+      *reinterpret_cast<uint2*>(j.perm16 + (int64_t)ada_perm_row(sr, j.W) * j.cols + k) = pk;
+    }
+    if (j.perm32) {
+      const int e = (int)(4 * i);
+      j.perm32[ada_perm_row(e, j.W)] = v.x; j.perm32[ada_perm_row(e + 1, j.W)] = v.y;
+      j.perm32[ada_perm_row(e + 2, j.W)] = v.z; j.perm32[ada_perm_row(e + 3, j.W)] = v.w;
+    }
+  }
+  for (int64_t i = 4 * n4 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < j.n; i += (int64_t)gridDim.x * blockDim.x) {
+    const float v = j.src[i];
+    j.dst32[i] = v;
+    if (j.dst16) j.dst16[i] = __float2bfloat16_rn(v);
+    if (j.perm16) {
+      const int sr = (int)(i / j.cols);
+      j.perm16[(int64_t)ada_perm_row(sr, j.W) * j.cols + (i - (int64_t)sr * j.cols)] = __float2bfloat16_rn(v);
+    }
+    if (j.perm32) j.perm32[ada_perm_row((int)i, j.W)] = v;
+  }
+}
+
 template <typename TO>
 __global__ void k_convert(const float* __restrict__ src, TO* __restrict__ dst, int64_t n) {
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
