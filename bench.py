@@ -217,6 +217,10 @@ def measure_train(dev, world, B=16, iters=5, warmup=2):
 
     vid, act = make_head(dev), make_act_head(dev)
     act.overlap_with(vid)  # what patch() sets up inside a MAR: the action head runs beside the video head
+    if world > 1 and os.environ.get("UVA_EARLY_ALLREDUCE", "1") != "0":
+        from unified_video_action_b200 import overlap_allreduce
+
+        overlap_allreduce([vid, act])  # each head's all-reduce starts when its own backward ends
     g = torch.Generator(device=dev).manual_seed(4321)
     z = torch.randn(B, 1024, Z, generator=g, device=dev, requires_grad=True)
     target = 0.2325 * torch.randn(B, 1024, C, generator=g, device=dev)

@@ -67,6 +67,25 @@ def _worker(rank, world, port, out_dir):
         for k, p in head.net.named_parameters():
             scale = float(want[k].abs().max())
             assert float((p.grad - want[k]).abs().max()) <= 1e-6 * max(scale, 1e-30), k
+        # the same step with the all-reduce started from inside the backward (overlap_allreduce)
+        from unified_video_action_b200 import overlap_allreduce
+
+        overlap_allreduce([head])
+        for p in head.net.parameters():
+            p.grad = None
+        z.grad = None
+        torch.manual_seed(7 + rank)
+        head(target, z, mask).backward()
+        assert head.net._grad_sync.pending is not None
+        assert allreduce_head_grads([head]) == 1
+        torch.cuda.synchronize()
+        for k, p in head.net.named_parameters():
+            scale = float(want[k].abs().max())
+            assert float((p.grad - want[k]).abs().max()) <= 1e-5 * max(scale, 1e-30), ("early", k)
+        # with gradient accumulation into existing .grad the early start must stand down
+        torch.manual_seed(7 + rank)
+        head(target, z, mask).backward()
+        assert head.net._grad_sync.pending is None
         open(os.path.join(out_dir, f"ok{rank}"), "w").write("ok")
     finally:
         dist.destroy_process_group()

@@ -328,6 +328,19 @@ class GradComm:
         self._c = c
         self.device = torch.device("cuda", torch.cuda.current_device())
 
+    def all_reduce_async(self, flat: torch.Tensor, average: bool = True) -> "torch.cuda.Event":
+        """The same collective on this communicator's own stream, behind everything already enqueued on the
+        caller's stream; returns the event a consumer of ``flat`` has to wait for.  All collectives of one
+        communicator go through this one stream, so they keep one order on every rank."""
+        dev = flat.device
+        if getattr(self, "_stream", None) is None:
+            self._stream = torch.cuda.Stream(device=dev, priority=-1)
+        self._stream.wait_event(torch.cuda.current_stream(dev).record_event())
+        with torch.cuda.stream(self._stream):
+            self.all_reduce_(flat, average)
+        flat.record_stream(self._stream)
+        return self._stream.record_event()
+
     def all_reduce_(self, flat: torch.Tensor, average: bool = True) -> torch.Tensor:
         if not flat.is_cuda or flat.dtype != torch.float32 or not flat.is_contiguous():
             raise RuntimeError("GradComm.all_reduce_: expected a contiguous fp32 CUDA tensor")

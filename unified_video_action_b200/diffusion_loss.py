@@ -176,7 +176,7 @@ class SimpleMLPAdaLN(nn.Module):
         new = cls.__new__(cls)
         memo[id(self)] = new
         for k, v in self.__dict__.items():
-            if k in ("_head", "_packed_key"):
+            if k in ("_head", "_packed_key", "_grad_sync"):
                 new.__dict__[k] = None
             else:
                 new.__dict__[k] = copy.deepcopy(v, memo)
@@ -210,6 +210,13 @@ class _FusedLoss(torch.autograd.Function):
             grads.append(flat[off:off + p.numel()].view(p.shape) if p.requires_grad else None)
             off += n
         dz = head.loss_bwd(dloss.float(), target, z, mask if ctx.has_mask else None, t, noise, grads)
+        sync = getattr(net, "_grad_sync", None)
+        if sync is not None:
+            # data-parallel training (patch.overlap_allreduce): the head's gradients are complete here, long before
+            # the backbone's backward is; start their all-reduce now on the communicator's stream.  Only when
+            # autograd will adopt `flat` as the .grad storage (no gradient accumulation into existing .grad).
+            if all(p.grad is None for p in params if p.requires_grad):
+                sync.launch(flat)
         return (None, None, dz.to(ctx.z_dtype) if ctx.needs_input_grad[2] else None, None, None, None, *grads)
 
 

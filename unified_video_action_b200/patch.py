@@ -99,11 +99,49 @@ def _reduce_flat(flat: torch.Tensor, group, average: bool, world: int) -> None:
         comm = _COMMS.get(key)
         if comm is None:
             comm = _COMMS[key] = _lib.GradComm(group)
-        comm.all_reduce_(flat, average)
+        if getattr(comm, "_stream", None) is not None:
+            # this communicator already runs collectives on its own stream (overlap_allreduce): keep them all there
+            torch.cuda.current_stream(flat.device).wait_event(comm.all_reduce_async(flat, average))
+        else:
+            comm.all_reduce_(flat, average)
         return
     dist.all_reduce(flat, group=group)
     if average:
         flat /= world
+
+
+class _GradSync:
+    """Per-head state of the early all-reduce: (flat gradient buffer, completion event) of the collective
+    that ``_FusedLoss.backward`` started."""
+
+    def __init__(self, group, average: bool):
+        self.group, self.average = group, average
+        self.pending = None
+
+    def comm(self, device):
+        from . import _lib
+
+        key = (id(self.group), device.index)
+        c = _COMMS.get(key)
+        if c is None:
+            c = _COMMS[key] = _lib.GradComm(self.group)
+        return c
+
+    def launch(self, flat: torch.Tensor) -> None:
+        self.pending = (flat, self.comm(flat.device).all_reduce_async(flat, self.average))
+
+
+def overlap_allreduce(heads: Iterable[nn.Module], group=None, average: bool = True) -> None:
+    """Start each head's gradient all-reduce from inside its backward ("issued from the extension
+    when the last wgrad tile lands, overlapped with the backbone's backward"): the fused backward of a head ends
+    long before the MAR decoder / encoder backward does, so the collective runs on the communicator's own stream
+    beside it.  ``allreduce_head_grads`` afterwards only waits for those collectives (and reduces what else the
+    head owns, e.g. the PyTorch pre-net).  Needs the NCCL process group to be initialised; ``None`` heads or
+    ``heads=[]`` are fine.  Call once after ``patch()``."""
+    for head in heads:
+        net = getattr(head, "net", None)
+        if net is not None:
+            net._grad_sync = _GradSync(group, average)
 
 
 def allreduce_head_grads(heads: Iterable[nn.Module], group=None, average: bool = True) -> int:
@@ -123,6 +161,14 @@ def allreduce_head_grads(heads: Iterable[nn.Module], group=None, average: bool =
         groups = {}
         for g in grads:
             groups.setdefault(g.untyped_storage().data_ptr(), []).append(g)
+        # a collective that the backward already started on this head's flat buffer: only wait for it
+        sync = getattr(getattr(head, "net", None), "_grad_sync", None)
+        if sync is not None and sync.pending is not None:
+            flat0, done = sync.pending
+            sync.pending = None
+            if groups.pop(flat0.untyped_storage().data_ptr(), None) is not None:
+                torch.cuda.current_stream(flat0.device).wait_event(done)
+                n += 1
         loose = []
         for members in groups.values():
             flat = _shared_flat(members) if len(members) > 1 else None
