@@ -432,6 +432,44 @@ def test_chain_kernel_cluster_staging_equals_plain_grid(video, monkeypatch):
         assert torch.equal(outs["1"], outs["4"]), (N, float((outs["1"] - outs["4"]).abs().max()))
 
 
+def test_fused_final_layer_ddpm_equals_two_kernels(video, monkeypatch):
+    """The final linear with the DDPM update (CFG mix, learned-range variance, x0-from-eps, clip, posterior mean,
+    temperature-scaled noise) in its epilogue gives the bits of final linear + k_ddpm_step: chunked path with CFG
+    (half not a multiple of the 128-row tile, so the uncond box starts at an odd row), without CFG with a ragged
+    tail, in-kernel Philox noise, and the CUDA-graph path (N = 300)."""
+    dev, g, P = video
+    heads = {}
+    for flag in ("0", "1"):
+        monkeypatch.setenv("UVA_FUSE_DDPM", flag)
+        heads[flag] = _head(16, 768, 1024, 6, P, 1, dev)
+    gen = torch.Generator().manual_seed(44)
+    cases = ((6000, 3.0, False, 3, False), (5001, 1.0, True, 3, False), (4098, 2.0, True, 2, True), (300, 1.0, True, 7, False),
+             (256, 3.0, False, 5, False))
+    for N, cfg, clip, k_end, philox in cases:
+        z = torch.randn(N, 768, generator=gen).to(dev)
+        x0 = torch.randn(N, 16, generator=gen).to(dev)
+        if cfg != 1.0:
+            x0[N // 2:] = x0[:N // 2]
+        nz = None if philox else torch.randn(k_end, N, 16, generator=gen).to(dev)
+        outs = {}
+        for flag, h in heads.items():
+            for rep in range(2 if N <= 1024 else 1):  # second call of the small path replays the captured graph
+                outs[flag] = h.sample(z, x0, nz, temperature=0.95, cfg=cfg, clip_denoised=clip, k_begin=0, k_end=k_end,
+                                      seed=77 if philox else None, offset=3)
+            torch.cuda.synchronize()
+        assert bool(torch.isfinite(outs["1"]).all())
+        assert torch.equal(outs["0"], outs["1"]), (N, cfg, float((outs["0"] - outs["1"]).abs().max()))
+    # one launch less per denoise step
+    N = 4096
+    z, x0, nz = torch.randn(N, 768, generator=gen).to(dev), torch.randn(N, 16, generator=gen).to(dev), torch.randn(1, N, 16, generator=gen).to(dev)
+    counts = {}
+    for flag, h in heads.items():
+        l0 = h.launch_count()
+        h.sample(z, x0, nz, k_begin=0, k_end=1)
+        counts[flag] = h.launch_count() - l0
+    assert counts["1"] < counts["0"], counts
+
+
 def test_error_paths(video):
     dev, g, P = video
     from unified_video_action_b200 import _lib

@@ -417,6 +417,26 @@ __global__ void k_philox_fill(PhiloxSeed s, uint32_t step0, int64_t per_step, in
   }
 }
 
+// x_{i-1} of one element from the (CFG-mixed) eps, the variance channel v, x_i and the noise draw (from memory at
+// `noise[e]`, or Philox element e): learned-range variance GD:283-291, x0-from-eps GD:348-353 (+ clip GD:293-297),
+// posterior mean GD:238-258, ancestral step GD:431-444 with the temperature scaling.  Shared by k_ddpm_step and
+// the fused final-layer epilogue (final_ddpm.cuh) so that both give the same bits.
+__device__ __forceinline__ float ddpm_update(float eps, float v, float x, const float* __restrict__ noise,
+                                             const PhiloxSeed& ps, uint32_t step, int64_t e, float temperature,
+                                             int clip, const StepCoef& k) {
+  const float frac = (v + 1.0f) / 2.0f;
+  const float logvar = frac * k.max_log + (1.0f - frac) * k.min_log;
+  float x0 = k.sqrt_recip * x - k.sqrt_recipm1 * eps;
+  if (clip) x0 = fminf(fmaxf(x0, -1.0f), 1.0f);
+  const float mean = k.coef1 * x0 + k.coef2 * x;
+  float out = mean;
+  if (k.nonzero) {
+    const float nz = ps.on ? philox_normal(ps, step, (uint64_t)e) : noise[e];
+    out = mean + expf(0.5f * logvar) * nz * temperature;
+  }
+  return out;
+}
+
 __global__ void k_ddpm_step(const float* __restrict__ net, int ldn, const float* __restrict__ x_cur,
                             const float* __restrict__ noise, float* __restrict__ x_next, int64_t rows,
                             int C, int64_t half, int64_t g0, int64_t ghalf, float cfg,
@@ -437,20 +457,9 @@ __global__ void k_ddpm_step(const float* __restrict__ net, int ldn, const float*
       eps = net[r * ldn + c];
     }
     const float v = net[r * ldn + C + c];
-    const float x = x_cur[i];
-    const float frac = (v + 1.0f) / 2.0f;
-    const float logvar = frac * k.max_log + (1.0f - frac) * k.min_log;
-    float x0 = k.sqrt_recip * x - k.sqrt_recipm1 * eps;
-    if (clip) x0 = fminf(fmaxf(x0, -1.0f), 1.0f);
-    const float mean = k.coef1 * x0 + k.coef2 * x;
-    float out = mean;
-    if (k.nonzero) {
-      // noise lives in the caller's [N, C] layout: chunk-local row r -> global row
-      const int64_t gr = g0 + ((half > 0 && r >= half) ? ghalf + (r - half) : r);
-      const float nz = ps.on ? philox_normal(ps, step, (uint64_t)(gr * C + c)) : noise[gr * C + c];
-      out = mean + expf(0.5f * logvar) * nz * temperature;
-    }
-    x_next[i] = out;
+    // noise lives in the caller's [N, C] layout: chunk-local row r -> global row
+    const int64_t gr = g0 + ((half > 0 && r >= half) ? ghalf + (r - half) : r);
+    x_next[i] = ddpm_update(eps, v, x_cur[i], noise, ps, step, gr * C + c, temperature, clip, k);
   }
 }
 

@@ -22,6 +22,7 @@
 #include "umma_gemm.cuh"
 #include "umma_gemm2.cuh"
 #include "chain_kernel.cuh"
+#include "final_ddpm.cuh"
 #include "optim.cuh"
 
 using namespace uva;
@@ -175,6 +176,17 @@ struct UvaHead {
   bool quad = false;  // UVA_QUAD: clusters of two CTA pairs with multicast A boxes (forward-form GEMMs)
   bool fuse_ln = true;  // UVA_FUSE_LN: LayerNorm-modulate inside the AdaLN GEMM epilogue (bf16 sampling path)
   int grid_mult = 1;  // UVA_GRID_MULT: GEMM grids of grid_mult x #SMs CTAs (block scheduler balances the tail)
+  // set by the sampler around run_stack: the final linear then runs with the DDPM update in its epilogue
+  // (final_ddpm.cuh) instead of writing the net output (bf16 mode; UVA_FUSE_DDPM=0 keeps the two kernels)
+  struct FinalFuse {
+    bool on = false;
+    const float* x_cur = nullptr; float* x_next = nullptr; const float* noise = nullptr;
+    PhiloxSeed ps{0, 0, 0, 0}; uint32_t step = 0;
+    int64_t half = 0, g0 = 0, ghalf = 0;
+    float cfg = 1.f, temperature = 1.f; int clip = 0;
+    StepCoef kc{};
+  } fin;
+  bool fuse_ddpm = true;
   PhiloxSeed noise{0, 0, 0, 0};  // uva_head_set_noise_seed: generator of the sampler's noise when step_noise == NULL
   int dbg_skip = 0;  // UVA_DEBUG_SKIP (timing diagnosis only, results are wrong): 1 = no GEMM launches, 2 = no row kernels
   // latency path (head_small.inc): small batches run with the AdaLN modulation of all denoise steps
@@ -318,6 +330,7 @@ extern "C" int uva_head_create(const UvaHeadDesc* desc, UvaHead** out) {
   if (const char* e = getenv("UVA_CHAIN")) h->use_chain = atoi(e) != 0;
   if (const char* e = getenv("UVA_CHAIN_ROWS")) { long v = atol(e); if (v >= 1 && v <= 128) h->chain_rows = v; }
   if (const char* e = getenv("UVA_BN32")) h->bn32 = atoi(e) != 0;
+  if (const char* e = getenv("UVA_FUSE_DDPM")) h->fuse_ddpm = atoi(e) != 0;
   if (const char* e = getenv("UVA_GRID_MULT")) { int v = atoi(e); if (v >= 1 && v <= 64) h->grid_mult = v; }
   CUDA_TRY(cudaStreamCreateWithFlags(&h->side, cudaStreamNonBlocking));
   CUDA_TRY(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
