@@ -358,6 +358,99 @@ k_lnmod_generic(const float* __restrict__ h, const float* __restrict__ ln_w,
 }
 
 // ------------------------------------------------------------------------------------------
+// Latency path (rows <= 1024, W = 1024): input_proj (DL:268) and the LayerNorm-modulate of the first ResBlock
+// (DL:163-165) in one kernel.  One block = IPL_ROWS rows x all W columns (thread t owns columns 4t .. 4t+3 and
+// keeps their input_proj weights in registers), so the row statistics are a block reduction: h = x . Wi^T + bi
+// is written as the fp32 residual stream and a = LN(h) * ln_w + ln_b) * (1 + scale) + shift as the bf16 operand of
+// the first GEMM.  Same two-pass statistics as k_lnmod.  Saves one dependent launch per denoise step and spreads
+// the projection over rows / 8 blocks instead of rows / 64.
+// ------------------------------------------------------------------------------------------
+constexpr int IPL_ROWS = 8;
+__global__ void __launch_bounds__(256)
+k_input_proj_lnmod(const float* __restrict__ x, const float* __restrict__ Wi, const float* __restrict__ bi,
+                   float* __restrict__ h, bf16* __restrict__ a, const float* __restrict__ ln_w,
+                   const float* __restrict__ ln_b, const bf16* __restrict__ shift, const bf16* __restrict__ scale,
+                   int64_t ldmod, int64_t rows, int C, int64_t half) {
+  constexpr int W = 1024;
+  __shared__ __align__(16) float xs[IPL_ROWS][16];
+  __shared__ float red[2][IPL_ROWS][8];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int64_t r0 = (int64_t)blockIdx.x * IPL_ROWS;
+  const int nr = (rows - r0 < IPL_ROWS) ? (int)(rows - r0) : IPL_ROWS;
+  if (tid < IPL_ROWS * 16) {
+    const int rr = tid >> 4, c = tid & 15;
+    float v = 0.f;
+    if (rr < nr && c < C) {
+      const int64_t r = r0 + rr;
+      const int64_t rs = (half > 0 && r >= half) ? (r - half) : r;
+      v = __ldg(x + rs * C + c);
+    }
+    xs[rr][c] = v;
+  }
+  const int j0 = tid * 4;
+  float w[4][16], b[4];
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    b[q] = __ldg(bi + j0 + q);
+#pragma unroll
+    for (int c = 0; c < 16; ++c) w[q][c] = (c < C) ? __ldg(Wi + (int64_t)(j0 + q) * C + c) : 0.f;
+  }
+  // issued early: the modulation and LayerNorm vectors of this thread's columns
+  const float4 g4 = __ldg(reinterpret_cast<const float4*>(ln_w + j0));
+  const float4 b4 = __ldg(reinterpret_cast<const float4*>(ln_b + j0));
+  __syncthreads();
+  float acc[IPL_ROWS][4];
+#pragma unroll
+  for (int rr = 0; rr < IPL_ROWS; ++rr) {
+#pragma unroll
+    for (int q = 0; q < 4; ++q) acc[rr][q] = b[q];
+#pragma unroll
+    for (int c = 0; c < 16; ++c) {
+      const float xv = xs[rr][c];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) acc[rr][q] = fmaf(xv, w[q][c], acc[rr][q]);
+    }
+    const float s = warp_sum((acc[rr][0] + acc[rr][1]) + (acc[rr][2] + acc[rr][3]));
+    if (lane == 0) red[0][rr][warp] = s;
+  }
+  __syncthreads();
+  float mean[IPL_ROWS];
+#pragma unroll
+  for (int rr = 0; rr < IPL_ROWS; ++rr) {
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) s += red[0][rr][i];
+    mean[rr] = s * (1.0f / W);
+    const float d0 = acc[rr][0] - mean[rr], d1 = acc[rr][1] - mean[rr], d2 = acc[rr][2] - mean[rr], d3 = acc[rr][3] - mean[rr];
+    const float qv = warp_sum((d0 * d0 + d1 * d1) + (d2 * d2 + d3 * d3));
+    if (lane == 0) red[1][rr][warp] = qv;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int rr = 0; rr < IPL_ROWS; ++rr) {
+    if (rr < nr) {
+      float qs = 0.f;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) qs += red[1][rr][i];
+      const float rstd = rsqrtf(qs * (1.0f / W) + 1e-6f);
+      const int64_t r = r0 + rr;
+      *reinterpret_cast<float4*>(h + r * W + j0) = make_float4(acc[rr][0], acc[rr][1], acc[rr][2], acc[rr][3]);
+      const uint2 us = *reinterpret_cast<const uint2*>(shift + r * ldmod + j0);
+      const uint2 uc = *reinterpret_cast<const uint2*>(scale + r * ldmod + j0);
+      const float2 s01 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&us.x));
+      const float2 s23 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&us.y));
+      const float2 c01 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&uc.x));
+      const float2 c23 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&uc.y));
+      const float n0 = (acc[rr][0] - mean[rr]) * rstd * g4.x + b4.x, n1 = (acc[rr][1] - mean[rr]) * rstd * g4.y + b4.y;
+      const float n2 = (acc[rr][2] - mean[rr]) * rstd * g4.z + b4.z, n3 = (acc[rr][3] - mean[rr]) * rstd * g4.w + b4.w;
+      *reinterpret_cast<uint2*>(a + r * W + j0) =
+          make_uint2(pack_bf16x2(n0 * (1.0f + c01.x) + s01.x, n1 * (1.0f + c01.y) + s01.y),
+                     pack_bf16x2(n2 * (1.0f + c23.x) + s23.x, n3 * (1.0f + c23.y) + s23.y));
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------
 // One DDPM ancestral step on the net output (p_mean_variance GD:260-346 for LEARNED_RANGE /
 // EPSILON, q_posterior_mean_variance GD:238-258, p_sample GD:395-444) with the CFG mix of
 // forward_with_cfg (DL:288-293) and the temperature scaling folded in.
