@@ -36,6 +36,13 @@ __device__ __forceinline__ float dsilu_f(float x) {
   return s * (1.0f + x * (1.0f - s));
 }
 
+// Programmatic dependent launch (latency path): a kernel launched with the programmatic-serialization attribute may
+// start while its predecessor in the stream is still running; griddep_wait() returns once the predecessor grid has
+// completed and its writes are visible, griddep_launch() lets the NEXT kernel start its own prologue now.  Both are
+// no-ops for a kernel launched the ordinary way.
+__device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void griddep_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

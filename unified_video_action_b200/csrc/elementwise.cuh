@@ -266,6 +266,8 @@ k_lnmod(const float* __restrict__ h, const float* __restrict__ ln_w, const float
         const TA* __restrict__ shift, const TA* __restrict__ scale, int64_t ldmod,
         TA* __restrict__ a, float* __restrict__ stats, int64_t rows) {
   constexpr int W = NV * 128;
+  griddep_wait();
+  griddep_launch();
   const int lane = threadIdx.x & 31;
   const int64_t warp_global = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int64_t warps_total = ((int64_t)gridDim.x * blockDim.x) >> 5;
@@ -377,6 +379,8 @@ k_input_proj_lnmod(const float* __restrict__ x, const float* __restrict__ Wi, co
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int64_t r0 = (int64_t)blockIdx.x * IPL_ROWS;
   const int nr = (rows - r0 < IPL_ROWS) ? (int)(rows - r0) : IPL_ROWS;
+  griddep_wait();
+  griddep_launch();
   if (tid < IPL_ROWS * 16) {
     const int rr = tid >> 4, c = tid & 15;
     float v = 0.f;
@@ -390,7 +394,7 @@ k_input_proj_lnmod(const float* __restrict__ x, const float* __restrict__ Wi, co
   const int j0 = tid * 4;
   float w[4][16], b[4];
 #pragma unroll
-  for (int q = 0; q < 4; ++q) {
+  for (int q = 0; q < 4; ++q) {  // weights do not depend on the previous kernel: loaded before griddep_wait
     b[q] = __ldg(bi + j0 + q);
 #pragma unroll
     for (int c = 0; c < 16; ++c) w[q][c] = (c < C) ? __ldg(Wi + (int64_t)(j0 + q) * C + c) : 0.f;

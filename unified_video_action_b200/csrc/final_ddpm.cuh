@@ -88,6 +88,8 @@ umma_final_ddpm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  griddep_wait();
+  griddep_launch();
 
   if (warp == 0) {
     if (elect_one()) {

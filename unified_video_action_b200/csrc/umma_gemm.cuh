@@ -235,6 +235,8 @@ umma_gemm_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  griddep_wait();    // (programmatic dependent launch: everything above overlapped the previous kernel's tail)
+  griddep_launch();  // after the wait: triggering before it (next kernel two ahead) measured slower
 
   if (warp == 0) {
     // ===================== TMA producer =====================

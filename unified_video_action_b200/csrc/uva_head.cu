@@ -187,6 +187,8 @@ struct UvaHead {
     StepCoef kc{};
   } fin;
   bool fuse_ddpm = true;
+  bool pdl = true;       // UVA_PDL: programmatic dependent launch between the per-step kernels of the latency path
+  bool pdl_now = false;  // set while the latency path enqueues its chain
   bool fuse_inproj = true;  // UVA_FUSE_INPROJ: input_proj + first LayerNorm-modulate in one kernel on the latency path
   PhiloxSeed noise{0, 0, 0, 0};  // uva_head_set_noise_seed: generator of the sampler's noise when step_noise == NULL
   int dbg_skip = 0;  // UVA_DEBUG_SKIP (timing diagnosis only, results are wrong): 1 = no GEMM launches, 2 = no row kernels
@@ -333,6 +335,7 @@ extern "C" int uva_head_create(const UvaHeadDesc* desc, UvaHead** out) {
   if (const char* e = getenv("UVA_BN32")) h->bn32 = atoi(e) != 0;
   if (const char* e = getenv("UVA_FUSE_DDPM")) h->fuse_ddpm = atoi(e) != 0;
   if (const char* e = getenv("UVA_FUSE_INPROJ")) h->fuse_inproj = atoi(e) != 0;
+  if (const char* e = getenv("UVA_PDL")) h->pdl = atoi(e) != 0;
   if (const char* e = getenv("UVA_GRID_MULT")) { int v = atoi(e); if (v >= 1 && v <= 64) h->grid_mult = v; }
   CUDA_TRY(cudaStreamCreateWithFlags(&h->side, cudaStreamNonBlocking));
   CUDA_TRY(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
