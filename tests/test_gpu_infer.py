@@ -470,6 +470,28 @@ def test_fused_final_layer_ddpm_equals_two_kernels(video, monkeypatch):
     assert counts["1"] < counts["0"], counts
 
 
+def test_noise_graph_keeps_the_reference_rng_stream(monkeypatch):
+    """DiffActLoss.sample in the latency regime replays the 100 per-step randn draws from a CUDA graph; the numbers
+    (and the generator state left behind) must be those of 100 eager torch.randn calls, i.e. the reference's
+    RNG stream (GD:431), call after call."""
+    dev = _cuda()
+    from unified_video_action_b200.diffusion_loss import _step_noise
+
+    for N, C in ((16, 2), (896, 2), (16, 10)):
+        torch.manual_seed(1234)
+        monkeypatch.setenv("UVA_NOISE_GRAPH", "0")
+        e1 = _step_noise(dev, 100, N, C).clone()
+        e2 = _step_noise(dev, 100, N, C).clone()
+        tail_e = torch.randn(5, device=dev)
+        torch.manual_seed(1234)
+        monkeypatch.setenv("UVA_NOISE_GRAPH", "1")
+        g1 = _step_noise(dev, 100, N, C).clone()  # first call captures, then replays
+        g2 = _step_noise(dev, 100, N, C).clone()
+        tail_g = torch.randn(5, device=dev)
+        assert torch.equal(e1, g1) and torch.equal(e2, g2) and torch.equal(tail_e, tail_g), (N, C)
+        assert not torch.equal(g1, g2)
+
+
 def test_error_paths(video):
     dev, g, P = video
     from unified_video_action_b200 import _lib

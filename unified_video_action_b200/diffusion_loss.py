@@ -259,6 +259,39 @@ class DiffLoss(nn.Module):
         return sample_rows(self.net, z, self.in_channels, self.num_sampling_steps, temperature, cfg, clip_denoised=False)
 
 
+_NOISE_GRAPHS: dict = {}  # (device index, steps, N, C) -> (CUDAGraph, static [steps, N, C] buffer), latency regime only
+
+
+def _step_noise(dev, steps: int, N: int, C: int) -> torch.Tensor:
+    """The ``steps`` per-step draws ``randn(N, C)`` of the reference loop (GD:431), in the reference's order on
+    torch's CUDA generator.  For small batches (predict_action: N = 16) the 100 launches cost more than the
+    whole denoise chain's arithmetic, so they are captured once per shape into a CUDA graph and replayed:
+    torch registers the generator with the graph, a replay consumes the same Philox offsets as the eager
+    calls would, hence the same numbers (tests/test_gpu_infer.py).  ``UVA_NOISE_GRAPH=0`` disables it."""
+    if N * C > 32768 or steps < 8 or os.environ.get("UVA_NOISE_GRAPH", "1") == "0":
+        out = torch.empty(steps, N, C, dtype=torch.float32, device=dev)
+        for k in range(steps):
+            torch.randn(N, C, out=out[k])
+        return out
+    key = (dev.index, steps, N, C)
+    entry = _NOISE_GRAPHS.get(key)
+    if entry is None:
+        if len(_NOISE_GRAPHS) >= 8:
+            _NOISE_GRAPHS.pop(next(iter(_NOISE_GRAPHS)))
+        buf = torch.empty(steps, N, C, dtype=torch.float32, device=dev)
+        graph = torch.cuda.CUDAGraph()
+        gen = torch.cuda.default_generators[dev.index]
+        state = gen.get_state()
+        with torch.cuda.graph(graph):
+            for k in range(steps):
+                torch.randn(N, C, out=buf[k])
+        gen.set_state(state)  # capture itself must not consume the stream
+        entry = _NOISE_GRAPHS[key] = (graph, buf)
+    graph, buf = entry
+    graph.replay()
+    return buf
+
+
 @torch.no_grad()
 def sample_rows(net: SimpleMLPAdaLN, z, C: int, steps: int, temperature: float, cfg: float, clip_denoised: bool):
     """The sampling tail shared by DiffLoss.sample (DL:68-90) and DiffActLoss.sample (DAL:207-227):
@@ -279,8 +312,6 @@ def sample_rows(net: SimpleMLPAdaLN, z, C: int, steps: int, temperature: float, 
         with torch.cuda.device(dev):
             return net.head().sample(z, noise, None, temperature=temperature, cfg=cfg, clip_denoised=clip_denoised, seed=seed)
     # one CUDA randn per step, as th.randn_like(x) inside p_sample (GD:431)
-    step_noise = torch.empty(steps, N, C, dtype=torch.float32, device=dev)
-    for k in range(steps):
-        torch.randn(N, C, out=step_noise[k])
+    step_noise = _step_noise(dev, steps, N, C)
     with torch.cuda.device(dev):
         return net.head().sample(z, noise, step_noise, temperature=temperature, cfg=cfg, clip_denoised=clip_denoised)
