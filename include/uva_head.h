@@ -176,6 +176,13 @@ int uva_nccl_comm_create(int32_t world_size, int32_t rank, const void* id128 /*h
 int uva_nccl_comm_destroy(void* comm);
 int uva_head_allreduce_grads(void* comm, float* flat, int64_t count, int32_t average, void* stream);
 
+/* Joint training step (MAR:770-784): the video head (16 384 rows) and the action head (256 rows) are independent
+ * and run on two streams.  The video head's persistent GEMM grids would take every SM, so the small head could
+ * only run between them; with a reserve of `sms` SMs (e.g. 16) the large head's loss_fwd / loss_bwd size their
+ * grids for num_sms - sms and the small head's kernels run beside them.  0 = use every SM (default).  Sampling
+ * and calls with <= 1024 rows are not affected. */
+int uva_head_set_train_reserve(UvaHead* h, int32_t sms);
+
 /* Number of kernel launches this handle has enqueued so far (bench.py's gpu_launches). */
 int64_t uva_head_launch_count(const UvaHead* h);
 

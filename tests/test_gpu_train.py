@@ -328,6 +328,22 @@ def test_action_head_side_stream_equals_serial(video, monkeypatch):
                 {k: prm.grad.clone() for m, tag in ((vid, "v."), (act, "a.")) for k, prm in ((tag + n, q) for n, q in m.named_parameters())})
 
     lv0, la0, dz0, g_ser = run("0")
+    vid.net.eager_backward = True  # opt-in: the big head's backward is enqueued with its forward (d loss = 1), scaled later
+    lvn, lan, dzn, g_non = run("0")
+    assert lvn == lv0 and lan == la0
+    _check(dzn.cpu(), dz0.cpu(), 0, "dz eager vs autograd-time backward")
+    for k in g_ser:
+        _check(g_non[k].cpu(), g_ser[k].cpu(), 0, k)
+    # d loss != 1 (loss scaling): the eager gradients are scaled afterwards
+    for prm in vid.parameters():
+        prm.grad = None
+    zz = z0.clone().requires_grad_(True)
+    torch.manual_seed(99)
+    (vid(target, zz, mask) * 3.0).backward()
+    _check(vid.net.cond_embed.weight.grad.cpu(), 3.0 * g_ser["v.net.cond_embed.weight"].cpu(), 0, "scaled eager grads")
+    with torch.no_grad():  # no graph, no eager work
+        assert vid(target, z0, mask).requires_grad is False
+    vid.net.eager_backward = False
     for _ in range(3):  # repeated: a missing stream dependency shows up as a flaky mismatch
         lv1, la1, dz1, g_par = run("1")
         assert lv1 == lv0 and la1 == la0

@@ -74,7 +74,7 @@ SYMBOLS = [
     "uva_head_sample", "uva_head_loss_fwd", "uva_head_loss_bwd", "uva_head_launch_count",
     "uva_gemm_bf16_selftest", "uva_last_error", "uva_build_info", "uva_head_timing_enable", "uva_head_timing_read",
     "uva_adamw_ema_step", "uva_nccl_version", "uva_nccl_unique_id", "uva_nccl_comm_create", "uva_nccl_comm_destroy",
-    "uva_head_allreduce_grads", "uva_head_set_noise_seed", "uva_philox_normal",
+    "uva_head_allreduce_grads", "uva_head_set_noise_seed", "uva_philox_normal", "uva_head_set_train_reserve",
 ]
 
 
@@ -123,6 +123,8 @@ def lib() -> ctypes.CDLL:
         L.uva_head_set_noise_seed.argtypes = [vp, ctypes.c_uint64, ctypes.c_uint32, i32]
         L.uva_philox_normal.restype = ctypes.c_int
         L.uva_philox_normal.argtypes = [ctypes.c_uint64, ctypes.c_uint32, i32, i64, i64, vp, vp]
+        L.uva_head_set_train_reserve.restype = ctypes.c_int
+        L.uva_head_set_train_reserve.argtypes = [vp, i32]
         L.uva_nccl_version.restype = i32
         L.uva_nccl_version.argtypes = []
         L.uva_nccl_unique_id.restype = ctypes.c_int
@@ -204,6 +206,9 @@ class Head:
             self._ws[what] = ws
         return ws
 
+    def set_train_reserve(self, sms: int) -> None:
+        _check(lib().uva_head_set_train_reserve(self._h, int(sms)), "uva_head_set_train_reserve")
+
     def launch_count(self) -> int:
         return int(lib().uva_head_launch_count(self._h))
 
@@ -279,13 +284,14 @@ class Head:
                                        _stream()), "uva_head_loss_fwd")
         return (loss, rows) if want_rows else loss
 
-    def loss_bwd(self, dloss, target, z, mask, t, noise, dparams: Sequence[Optional[torch.Tensor]]):
+    def loss_bwd(self, dloss, target, z, mask, t, noise, dparams: Sequence[Optional[torch.Tensor]], dz=None):
         target, z, noise = _f32c(target, "target"), _f32c(z, "z"), _f32c(noise, "noise")
         mask = None if mask is None else _f32c(mask, "mask")
         dloss = _f32c(dloss.reshape(1), "dloss")
         t = t.to(device=z.device, dtype=torch.int64).contiguous()
         N = z.shape[0]
-        dz = torch.empty(N, self.Z, dtype=torch.float32, device=z.device)
+        if dz is None:
+            dz = torch.empty(N, self.Z, dtype=torch.float32, device=z.device)
         for g in dparams:
             if g is not None and (g.dtype != torch.float32 or not g.is_contiguous() or not g.is_cuda):
                 raise RuntimeError("gradient buffers must be contiguous fp32 CUDA tensors")

@@ -154,14 +154,22 @@ k_inproj_wgrad(const float* __restrict__ dh, const float* __restrict__ xt, float
 // Gated residual backward (DL:167: h' = h + gate * q):  dq = dh * gate, dgate = dh * q.
 // dh itself passes through unchanged (residual).  gate / dgate live in the modulation buffers.
 // ------------------------------------------------------------------------------------------
+// sum_dq / sum_dgate (may be null; only when the grid stride is a multiple of W / 4, i.e. every thread keeps its
+// four columns): the bias gradients  db2 += sum_r dq,  d(adaLN bias, gate part) += sum_r dgate  accumulated in
+// registers over the thread's rows and added with one atomic per column and thread — the two separate
+// column-sum passes over dq and dgate disappear.
 template <typename TA>
 __global__ void k_gate_bwd(const float* __restrict__ dh, const TA* __restrict__ gate, const TA* __restrict__ q,
-                           int64_t ldmod, TA* __restrict__ dq, TA* __restrict__ dgate, int64_t rows, int W) {
+                           int64_t ldmod, TA* __restrict__ dq, TA* __restrict__ dgate, int64_t rows, int W,
+                           float* __restrict__ sum_dq = nullptr, float* __restrict__ sum_dgate = nullptr) {
   const int wq = W / 4;
   const int64_t n = rows * wq;
+  float s1[4] = {0.f, 0.f, 0.f, 0.f}, s2[4] = {0.f, 0.f, 0.f, 0.f};
+  int jcol = -1;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     const int64_t r = i / wq;
     const int j = (int)(i - r * wq) * 4;
+    jcol = j;
     const float4 d = *reinterpret_cast<const float4*>(dh + r * W + j);
     float g[4], qq[4];
     load4<TA>(gate + r * ldmod + j, g);
@@ -170,6 +178,15 @@ __global__ void k_gate_bwd(const float* __restrict__ dh, const TA* __restrict__ 
     const float o2[4] = {d.x * qq[0], d.y * qq[1], d.z * qq[2], d.w * qq[3]};
     store4(dq + r * W + j, o1);
     store4(dgate + r * ldmod + j, o2);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { s1[k] += o1[k]; s2[k] += o2[k]; }
+  }
+  if (jcol >= 0) {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      if (sum_dq) atomicAdd(sum_dq + jcol + k, s1[k]);
+      if (sum_dgate) atomicAdd(sum_dgate + jcol + k, s2[k]);
+    }
   }
 }
 

@@ -143,14 +143,19 @@ k_loss_reduce(const float* __restrict__ row_loss, const float* __restrict__ mask
 }
 
 // d loss / d row_loss[r] = dloss * mask[r] / sum(mask) (or dloss / rows); scales the rows of dnet.
+// out_b (may be null): the same rows as the bf16 operand of the final layer's tensor-core backward; columns
+// >= c_valid (padding of the 32-wide net-output buffer) are written as zero.
 __global__ void k_dnet_scale(const float* __restrict__ dnet, const float* __restrict__ mask,
                              const float* __restrict__ denom, const float* __restrict__ dloss,
-                             float* __restrict__ out, int64_t rows, int ldn) {
+                             float* __restrict__ out, int64_t rows, int ldn, bf16* __restrict__ out_b = nullptr,
+                             int c_valid = 0) {
   const int64_t n = rows * ldn;
   const float g = dloss[0] / denom[0];
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     const int64_t r = i / ldn;
-    out[i] = dnet[i] * (mask ? mask[r] * g : g);
+    const float v = dnet[i] * (mask ? mask[r] * g : g);
+    out[i] = v;
+    if (out_b) out_b[i] = __float2bfloat16_rn(((int)(i - r * ldn) < c_valid) ? v : 0.f);
   }
 }
 

@@ -140,6 +140,8 @@ struct DevTables {  // fp32 device copies of one process' tables, [T] each
 struct UvaHead {
   UvaHeadDesc d;
   int num_sms = 148;
+  int gemm_sms = 148;       // SMs the persistent GEMM grids may take right now (num_sms, or less inside a training call)
+  int train_reserve = 0;    // uva_head_set_train_reserve: SMs left free during loss_fwd / loss_bwd for a head on another stream
   int64_t chunk_rows = 65536;
   int nmod = 0;  // (3*depth + 2) * W : width of the concatenated AdaLN modulation output
   ScheduleTables gen, train;
@@ -189,6 +191,8 @@ struct UvaHead {
   bool fuse_ddpm = true;
   bool pdl = true;       // UVA_PDL: programmatic dependent launch between the per-step kernels of the latency path
   bool pdl_now = false;  // set while the latency path enqueues its chain
+  bool fuse_colsum = true;  // UVA_FUSE_COLSUM: bias gradients of mlp.2 / gate modulation summed inside k_gate_bwd
+  bool final_tc = true;  // UVA_FINAL_TC: final-layer backward (dgrad K = 32, wgrad M = 2C) on the tcgen05 GEMMs
   bool fuse_inproj = true;  // UVA_FUSE_INPROJ: input_proj + first LayerNorm-modulate in one kernel on the latency path
   PhiloxSeed noise{0, 0, 0, 0};  // uva_head_set_noise_seed: generator of the sampler's noise when step_noise == NULL
   int dbg_skip = 0;  // UVA_DEBUG_SKIP (timing diagnosis only, results are wrong): 1 = no GEMM launches, 2 = no row kernels
@@ -206,6 +210,15 @@ struct UvaHead {
     cudaGraphExec_t exec; int64_t launches; int seen;
   };
   std::vector<SmallGraph> graphs;
+  // training calls on small batches (the action head: 16 rows per sample) are launch bound on the HOST (~140
+  // launches with their tensor maps per fwd + bwd): the second call with the same pointers captures a CUDA graph,
+  // later calls replay it.  Key = every pointer and size the enqueued work depends on.  UVA_TRAIN_GRAPH=0: off.
+  struct TrainGraph {
+    std::vector<uintptr_t> key;
+    cudaGraphExec_t exec; int64_t launches; int seen;
+  };
+  std::vector<TrainGraph> tgraphs;
+  bool train_graph = true;
   bool timing = false;
   int cur_cat = 0;
   struct TimedLaunch { int cat; cudaEvent_t a, b; };
@@ -249,6 +262,12 @@ extern "C" int uva_philox_normal(uint64_t seed, uint32_t offset, int32_t step0, 
   k_philox_fill<<<grid_for(n, 256, sms), 256, 0, (cudaStream_t)stream>>>(s, (uint32_t)step0, per_step, n, out);
   const cudaError_t e = cudaPeekAtLastError();
   if (e != cudaSuccess) return fail(UVA_ERR_CUDA, "philox_normal: %s", cudaGetErrorString(e));
+  return UVA_OK;
+}
+
+extern "C" int uva_head_set_train_reserve(UvaHead* h, int32_t sms) {
+  if (!h || sms < 0 || sms >= h->num_sms) return fail(UVA_ERR_INVALID, "set_train_reserve: bad argument");
+  h->train_reserve = sms / 2 * 2;
   return UVA_OK;
 }
 
@@ -318,6 +337,7 @@ extern "C" int uva_head_create(const UvaHeadDesc* desc, UvaHead** out) {
   UvaHead* h = new UvaHead();
   h->d = d;
   h->num_sms = prop.multiProcessorCount;
+  h->gemm_sms = h->num_sms;
   h->nmod = (3 * d.depth + 2) * d.W;
   if (const char* e = getenv("UVA_CHUNK_ROWS")) {
     long v = atol(e);
@@ -336,6 +356,9 @@ extern "C" int uva_head_create(const UvaHeadDesc* desc, UvaHead** out) {
   if (const char* e = getenv("UVA_FUSE_DDPM")) h->fuse_ddpm = atoi(e) != 0;
   if (const char* e = getenv("UVA_FUSE_INPROJ")) h->fuse_inproj = atoi(e) != 0;
   if (const char* e = getenv("UVA_PDL")) h->pdl = atoi(e) != 0;
+  if (const char* e = getenv("UVA_FINAL_TC")) h->final_tc = atoi(e) != 0;
+  if (const char* e = getenv("UVA_TRAIN_GRAPH")) h->train_graph = atoi(e) != 0;
+  if (const char* e = getenv("UVA_FUSE_COLSUM")) h->fuse_colsum = atoi(e) != 0;
   if (const char* e = getenv("UVA_GRID_MULT")) { int v = atoi(e); if (v >= 1 && v <= 64) h->grid_mult = v; }
   CUDA_TRY(cudaStreamCreateWithFlags(&h->side, cudaStreamNonBlocking));
   CUDA_TRY(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
@@ -437,6 +460,8 @@ extern "C" void uva_head_destroy(UvaHead* h) {
   cudaFree(h->temb_hidden_b); cudaFree(h->temb_pre_b); cudaFree(h->feat_b);
   cudaFree(h->wf); cudaFree(h->wb); cudaFree(h->adab_p); cudaFree(h->d_tsteps); cudaFree(h->d_coef);
   for (auto& g : h->graphs)
+    if (g.exec) cudaGraphExecDestroy(g.exec);
+  for (auto& g : h->tgraphs)
     if (g.exec) cudaGraphExecDestroy(g.exec);
   if (h->side) cudaStreamDestroy(h->side);
   if (h->ev_fork) cudaEventDestroy(h->ev_fork);

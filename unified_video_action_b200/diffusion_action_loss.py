@@ -109,6 +109,12 @@ class DiffActLoss(nn.Module):
         object.__setattr__(self, "_fork_from", None if other is None else weakref.ref(other))
         if other is not None:
             other._record_entry = True
+            # the big head can leave SMs to this head's kernels (UVA_TRAIN_RESERVE_SMS; measured: no gain, default 0)
+            other.net.train_reserve_sms = int(os.environ.get("UVA_TRAIN_RESERVE_SMS", "0"))
+            # ... and can differentiate eagerly (its backward enqueued with its forward on a third stream, see
+            # _FusedLoss; UVA_EAGER_BACKWARD=1).  Both were measured on the C2 step and change nothing (6.4 ms either
+            # way: the two heads' kernels add up rather than overlap), so both stay off by default.
+            other.net.eager_backward = os.environ.get("UVA_EAGER_BACKWARD", "0") != "0"
             quiet = getattr(torch.autograd.graph, "set_warn_on_accumulate_grad_stream_mismatch", None)
             if quiet is not None:  # parameters are created on the default stream and used on the side stream on purpose
                 quiet(False)

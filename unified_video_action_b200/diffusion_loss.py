@@ -22,6 +22,7 @@ from . import _lib
 # id(DiffLoss module) -> (weak reference to z, z._version, event recorded when its forward() was entered);
 # kept outside the modules so that copy.deepcopy (EMA) and state_dict never see CUDA events
 _ENTRY: dict = {}
+_EAGER_STREAMS: dict = {}  # device index -> stream of the eagerly enqueued backward (see _FusedLoss)
 
 
 def _mode_from(precision: Optional[str]) -> int:
@@ -117,6 +118,9 @@ class SimpleMLPAdaLN(nn.Module):
         self._head: Optional[_lib.Head] = None
         self._packed_key = None
         self._names = param_names(num_res_blocks)
+        self.eager_backward = False  # see _FusedLoss
+        self.train_reserve_sms = 0  # SMs this head leaves free during training for a head on another stream (overlap_with)
+        self._reserve_set = None
         self.device_noise: Optional[bool] = None  # True: in-kernel Philox step noise (default: UVA_B200_NOISE env, "torch")
 
     def initialize_weights(self):
@@ -140,8 +144,17 @@ class SimpleMLPAdaLN(nn.Module):
 
     # ---- library plumbing -------------------------------------------------------------------
     def ordered_params(self) -> List[torch.nn.Parameter]:
+        """The parameters in C-ABI order.  Cached: walking named_parameters() costs ~0.3 ms of Python per call and
+        the training step asks five times; the cache is dropped when a Parameter object is replaced (``_apply`` with
+        swapped tensors, manual re-assignment) — in-place updates (optimizer, load_state_dict, .to()) keep identity."""
+        cached = self.__dict__.get("_ordered")
+        if cached is not None and cached[0] is self.time_embed.mlp[0].weight and cached[-1] is self.final_layer.adaLN_modulation[1].bias \
+                and cached[4] is self.cond_embed.weight:
+            return cached
         d = dict(self.named_parameters())
-        return [d[n] for n in self._names]
+        cached = [d[n] for n in self._names]
+        self.__dict__["_ordered"] = cached
+        return cached
 
     def head(self) -> _lib.Head:
         """The CUDA head with up-to-date packed weights (re-packed when any parameter changed:
@@ -155,6 +168,10 @@ class SimpleMLPAdaLN(nn.Module):
                 self._head = _lib.Head(self.in_channels, self.z_channels, self.model_channels, self.num_res_blocks,
                                        self._T[0], self._T[1], self._mode)
                 self._packed_key = None
+                self._reserve_set = None
+            if self._reserve_set != self.train_reserve_sms:
+                self._head.set_train_reserve(self.train_reserve_sms)
+                self._reserve_set = self.train_reserve_sms
             key = tuple((p.data_ptr(), p._version) for p in params)
             if key != self._packed_key:
                 self._head.load_weights(params)
@@ -176,40 +193,82 @@ class SimpleMLPAdaLN(nn.Module):
         new = cls.__new__(cls)
         memo[id(self)] = new
         for k, v in self.__dict__.items():
-            if k in ("_head", "_packed_key", "_grad_sync"):
+            if k in ("_head", "_packed_key", "_grad_sync", "_ordered", "_reserve_set"):
                 new.__dict__[k] = None
             else:
                 new.__dict__[k] = copy.deepcopy(v, memo)
         return new
 
 
+def _grad_buffers(params, device):
+    """One zero-filled flat fp32 buffer + one view per parameter (a single memset instead of one fill per tensor)."""
+    sizes = [(p.numel() + 3) // 4 * 4 if p.requires_grad else 0 for p in params]
+    flat = torch.zeros(sum(sizes), dtype=torch.float32, device=device)
+    grads, off = [], 0
+    for p, n in zip(params, sizes):
+        grads.append(flat[off:off + p.numel()].view(p.shape) if p.requires_grad else None)
+        off += n
+    return flat, grads
+
+
 class _FusedLoss(torch.autograd.Function):
-    """training_losses + masked mean as one op with a hand-written backward (GD:746-818, DL:64-66)."""
+    """training_losses + masked mean as one op with a hand-written backward (GD:746-818, DL:64-66).
+
+    ``net.eager_backward`` (set by ``DiffActLoss.overlap_with`` on the big head of a joint step): the op's output is
+    the scalar loss, so its backward is linear in the incoming scalar gradient.  The whole backward is then enqueued
+    right behind the forward with d loss = 1 and ``backward()`` only scales the result by the real d loss.  Why:
+    autograd runs the head that was called LAST first, so in the joint step the host spends ~1.3 ms enqueueing the
+    small action head's backward before it gets to the 16 384-row head, whose GPU stream idles meanwhile."""
 
     @staticmethod
     def forward(ctx, net: SimpleMLPAdaLN, target, z, mask, t, noise, *params):
         head = net.head()
         loss = head.loss_fwd(target, z, mask, t, noise)
         ctx.net = net
-        ctx.save_for_backward(target, z, mask if mask is not None else torch.empty(0, device=z.device), t, noise)
         ctx.has_mask = mask is not None
         ctx.z_dtype = z.dtype
+        ctx.eager = None
+        if net.__dict__.pop("_eager_now", False):  # decided by the caller, where the grad mode is still visible
+            # on its own stream: whatever the caller enqueues next on its stream (the other heads' joins, the loss
+            # sum and ITS backward, which the small head's backward waits for) must not queue up behind 3 ms of GEMMs
+            plist = net.ordered_params()
+            dev = z.device
+            cur = torch.cuda.current_stream(dev)
+            flat, grads = _grad_buffers(plist, dev)
+            one = torch.ones(1, dtype=torch.float32, device=dev)
+            dz = torch.empty(z.shape[0], z.shape[1], dtype=torch.float32, device=dev)
+            es = _EAGER_STREAMS.get(dev.index)
+            if es is None:
+                es = _EAGER_STREAMS[dev.index] = torch.cuda.Stream(device=dev)
+            es.wait_event(cur.record_event())
+            with torch.cuda.stream(es):
+                head.loss_bwd(one, target, z, mask, t, noise, grads, dz=dz)
+            for tns in (flat, dz, one, target, z, t, noise) + ((mask,) if mask is not None else ()):
+                tns.record_stream(es)
+            ctx.eager = (flat, grads, dz, es.record_event())
+            ctx.save_for_backward()
+        else:
+            ctx.save_for_backward(target, z, mask if mask is not None else torch.empty(0, device=z.device), t, noise)
         return loss.reshape(())
 
     @staticmethod
     def backward(ctx, dloss):
-        target, z, mask, t, noise = ctx.saved_tensors
         net = ctx.net
-        head = net.head()
         params = net.ordered_params()
-        # one zero-filled flat buffer, one view per parameter (a single memset instead of one fill per tensor)
-        sizes = [(p.numel() + 3) // 4 * 4 if p.requires_grad else 0 for p in params]
-        flat = torch.zeros(sum(sizes), dtype=torch.float32, device=z.device)
-        grads, off = [], 0
-        for p, n in zip(params, sizes):
-            grads.append(flat[off:off + p.numel()].view(p.shape) if p.requires_grad else None)
-            off += n
-        dz = head.loss_bwd(dloss.float(), target, z, mask if ctx.has_mask else None, t, noise, grads)
+        if ctx.eager is not None:
+            flat, grads, dz, done = ctx.eager
+            ctx.eager = None  # a second backward through this node would scale twice
+            torch.cuda.current_stream(flat.device).wait_event(done)
+            g = dloss.float().reshape(1)
+            flat.mul_(g)
+            dz = dz.mul_(g)
+        else:
+            if not ctx.saved_tensors:
+                raise RuntimeError("DiffLoss: backward through an eagerly differentiated loss can run only once")
+            target, z, mask, t, noise = ctx.saved_tensors
+            head = net.head()
+            flat, grads = _grad_buffers(params, z.device)
+            dz = head.loss_bwd(dloss.float(), target, z, mask if ctx.has_mask else None, t, noise, grads)
         sync = getattr(net, "_grad_sync", None)
         if sync is not None:
             # data-parallel training (patch.overlap_allreduce): the head's gradients are complete here, long before
@@ -251,8 +310,11 @@ class DiffLoss(nn.Module):
         # same draws, same order as the reference: t (DL:51), then noise = randn_like(x_start) (GD:761)
         t = torch.randint(0, self.num_timesteps, (target.shape[0],), device=target.device)
         noise = torch.randn_like(target, dtype=torch.float32)
+        params = self.net.ordered_params()
+        if self.net.eager_backward and torch.is_grad_enabled() and (z.requires_grad or any(p.requires_grad for p in params)):
+            self.net.__dict__["_eager_now"] = True
         with torch.cuda.device(z.device):
-            return _FusedLoss.apply(self.net, target.float(), z, mask.float(), t, noise, *self.net.ordered_params())
+            return _FusedLoss.apply(self.net, target.float(), z, mask.float(), t, noise, *params)
 
     @torch.no_grad()
     def sample(self, z, temperature=1.0, cfg=1.0, text_latents=None):
