@@ -232,7 +232,11 @@ def measure_train(dev, world, B=16, iters=5, warmup=2):
             for p in m.parameters():
                 p.grad = None
         z.grad = None
-        loss = vid(target, z, mask) + act(actions, z)
+        # the reference trains under Accelerate's bf16 autocast (workspace/train_unified_video_action_workspace.py:
+        # mixed_precision), which is what the PyTorch pre-net of DiffActLoss (Conv2d 768->768 3x3 + Linears) sees;
+        # the heads themselves take fp32 tensors and compute in bf16 either way.  UVA_BENCH_AUTOCAST=0: fp32 pre-net.
+        with torch.autocast("cuda", dtype=torch.bfloat16, enabled=os.environ.get("UVA_BENCH_AUTOCAST", "1") != "0"):
+            loss = vid(target, z, mask) + act(actions, z)
         loss.backward()
         if world > 1:
             allreduce_head_grads([vid, act])
