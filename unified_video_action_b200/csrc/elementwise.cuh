@@ -172,10 +172,14 @@ __global__ void k_ysilu_steps(const float* __restrict__ cemb, const float* __res
 constexpr int IP_ROWS = 64;
 __global__ void __launch_bounds__(256)
 k_input_proj(const float* __restrict__ x, const float* __restrict__ Wi, const float* __restrict__ bi,
-             float* __restrict__ h, int64_t rows, int C, int W, int64_t half, float* __restrict__ stats) {
+             float* __restrict__ h, int64_t rows, int C, int W, int64_t half, float* __restrict__ stats,
+             int dup = 0) {
+  // dup (CFG, rows = 2 * half): the uncond row r + half has the input of the cond row r (DL:286-287), so a block
+  // covers rows of the first half only and writes every result (and its row sums) to both rows
   __shared__ __align__(16) float xs[IP_ROWS][16];  // the block's input rows, zero padded to 16 channels
   const int64_t r0 = (int64_t)blockIdx.x * IP_ROWS;
-  const int64_t left = rows - r0;
+  const int64_t left = (dup ? half : rows) - r0;
+  const int64_t twin = dup ? half : 0;
   const int nr = left < IP_ROWS ? (int)left : IP_ROWS;
   for (int i = threadIdx.x; i < IP_ROWS * 16; i += blockDim.x) {
     const int rr = i >> 4, c = i & 15;
@@ -233,6 +237,10 @@ k_input_proj(const float* __restrict__ x, const float* __restrict__ Wi, const fl
       const bool two = rr + 1 < nr;  // block-uniform
       *reinterpret_cast<float4*>(hp + (int64_t)rr * W) = make_float4(acc[0][0], acc[0][1], acc[0][2], acc[0][3]);
       if (two) *reinterpret_cast<float4*>(hp + (int64_t)(rr + 1) * W) = make_float4(acc[1][0], acc[1][1], acc[1][2], acc[1][3]);
+      if (twin) {
+        *reinterpret_cast<float4*>(hp + (twin + rr) * W) = make_float4(acc[0][0], acc[0][1], acc[0][2], acc[0][3]);
+        if (two) *reinterpret_cast<float4*>(hp + (twin + rr + 1) * W) = make_float4(acc[1][0], acc[1][1], acc[1][2], acc[1][3]);
+      }
       if (sp != nullptr) {  // row sums for the LayerNorm of the first block: one (sum, sum of squares) per 128 columns
         float s0 = (acc[0][0] + acc[0][1]) + (acc[0][2] + acc[0][3]);
         float q0 = (acc[0][0] * acc[0][0] + acc[0][1] * acc[0][1]) + (acc[0][2] * acc[0][2] + acc[0][3] * acc[0][3]);
@@ -248,6 +256,10 @@ k_input_proj(const float* __restrict__ x, const float* __restrict__ Wi, const fl
         if (lane == 0) {
           *reinterpret_cast<float2*>(sp + (int64_t)rr * (W / 128) * 2) = make_float2(s0, q0);
           if (two) *reinterpret_cast<float2*>(sp + (int64_t)(rr + 1) * (W / 128) * 2) = make_float2(s1, q1);
+          if (twin) {
+            *reinterpret_cast<float2*>(sp + (twin + rr) * (W / 128) * 2) = make_float2(s0, q0);
+            if (two) *reinterpret_cast<float2*>(sp + (twin + rr + 1) * (W / 128) * 2) = make_float2(s1, q1);
+          }
         }
       }
     }
