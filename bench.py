@@ -242,18 +242,24 @@ def measure_train(dev, world, B=16, iters=5, warmup=2):
             allreduce_head_grads([vid, act])
         return loss
 
-    for _ in range(warmup):
+    # at least 10 untimed steps: on a fresh box single steps up to the ~8th have been seen to stall for > 100 ms
+    # (lazy module loads of cuDNN / the allocator settling on its blocks, after which the graph replay of the small
+    # head starts); p50_ms / max_ms below show the spread of the timed steps
+    for _ in range(max(warmup, 10)):
         step()
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    marks = [torch.cuda.Event(enable_timing=True) for _ in range(iters)]
     e0.record()
-    for _ in range(iters):
+    for i in range(iters):
         loss = step()
+        marks[i].record()
     e1.record()
     torch.cuda.synchronize()
-    ms = e0.elapsed_time(e1) / iters
+    ms = e0.elapsed_time(e1) / iters  # the reported number: whole timed region / steps
+    per = sorted(a.elapsed_time(b) for a, b in zip([e0] + marks[:-1], marks))  # spread of the single steps
     rows = B * 1024 + B * 16
     # optimizer + EMA + operand re-pack of both heads: fused AdamW/EMA pass, then load_weights
     import copy
@@ -272,7 +278,7 @@ def measure_train(dev, world, B=16, iters=5, warmup=2):
     e1.record()
     torch.cuda.synchronize()
     opt_ms = e0.elapsed_time(e1) / iters
-    return {"ms_per_step": ms, "optimizer_ema_repack_ms": opt_ms, "rows_per_gpu": rows, "rows_per_s_per_gpu": rows / (ms / 1e3),
+    return {"ms_per_step": ms, "p50_ms": per[len(per) // 2], "max_ms": per[-1], "optimizer_ema_repack_ms": opt_ms, "rows_per_gpu": rows, "rows_per_s_per_gpu": rows / (ms / 1e3),
             "tflops_per_gpu": (B * 1024) * TRAIN_FLOP_PER_ROW / (ms / 1e3) / 1e12, "loss": float(loss.detach()),
             "what": f"DiffLoss fwd+bwd {B}x1024 rows + DiffActLoss fwd+bwd {B}x16 rows (incl. its PyTorch pre-net), bf16"}
 
