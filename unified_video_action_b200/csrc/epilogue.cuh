@@ -25,6 +25,9 @@ struct EpiArgs {
   const float* ln_b = nullptr;
   int32_t ln_tiles = 0;         // EPI_LNMOD: number of leading 256-column tiles that are (shift | scale) pairs
   int32_t ln_width = 0;         // EPI_LNMOD: W
+  // EPI_DSILU_ACT on the CTA-pair kernel: column sums of the fp32 result (the bias gradient of the Linear in front of
+  // the SiLU) are reduced over each warp's 32 rows with shuffles and added here with one atomic per column; null: off
+  float* colsum = nullptr;
 };
 
 enum EpiKind {

@@ -333,7 +333,7 @@ k_lnmod_bwd_generic(const TA* __restrict__ da, const float* __restrict__ h, cons
 // 16 bytes) columns; warp w takes rows w, w + 8, ... with 8 independent 16-byte loads in flight per lane,
 // the 8 warps are combined through shared memory and added with one atomic per column.
 // ------------------------------------------------------------------------------------------
-constexpr int CS_ROWS = 256;
+constexpr int CS_ROWS = 128;
 template <typename TI>
 __global__ void __launch_bounds__(256)
 k_colsum(const TI* __restrict__ X, int64_t ld, int64_t rows, int cols, float* __restrict__ out) {

@@ -507,10 +507,37 @@ umma_gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             for (int i = 0; i < 4; ++i) av[i] = *reinterpret_cast<const uint4*>(grow + ((i ^ rsw) << 4));
             tmem_ld_wait();
             const uint32_t* aw = reinterpret_cast<const uint32_t*>(av);
+            if (ep.colsum == nullptr) {
 #pragma unroll
-            for (int i = 0; i < 16; ++i) {
-              const float2 pq = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&aw[i]));
-              pk[i] = pack_bf16x2(__uint_as_float(v[2 * i]) * dsilu_tanh(pq.x), __uint_as_float(v[2 * i + 1]) * dsilu_tanh(pq.y));
+              for (int i = 0; i < 16; ++i) {
+                const float2 pq = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&aw[i]));
+                pk[i] = pack_bf16x2(__uint_as_float(v[2 * i]) * dsilu_tanh(pq.x), __uint_as_float(v[2 * i + 1]) * dsilu_tanh(pq.y));
+              }
+            } else {
+              // the same products, plus their column sums over the warp's 32 rows (rows past M are zero: TMA
+              // zero-fills both operands): a transposing butterfly, step k exchanges half of the live values with
+              // lane ^ (16 >> k) so that after 5 steps lane l holds the sum of column l -> 31 shuffles
+              // and adds per thread instead of 160, then one atomic per column and warp
+              float f[32];
+#pragma unroll
+              for (int i = 0; i < 16; ++i) {
+                const float2 pq = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&aw[i]));
+                f[2 * i] = __uint_as_float(v[2 * i]) * dsilu_tanh(pq.x);
+                f[2 * i + 1] = __uint_as_float(v[2 * i + 1]) * dsilu_tanh(pq.y);
+                pk[i] = pack_bf16x2(f[2 * i], f[2 * i + 1]);
+              }
+#pragma unroll
+              for (int half = 16; half >= 1; half >>= 1) {
+                const bool up = (lane & half) != 0;
+#pragma unroll
+                for (int i = 0; i < half; ++i) {
+                  const float give = up ? f[i] : f[i + half];
+                  const float keep = up ? f[i + half] : f[i];
+                  f[i] = keep + __shfl_xor_sync(0xffffffffu, give, half);
+                }
+              }
+              // lane bit `half` selected the upper half of the live columns at every step: lane l ends with column l
+              atomicAdd(ep.colsum + n_blk * BN + 32 * blk + lane, f[0]);
             }
           } else if constexpr (KIND == EPI_SILU_SAVE) {
             tmem_ld_wait();

@@ -191,6 +191,7 @@ struct UvaHead {
   bool fuse_ddpm = true;
   bool pdl = true;       // UVA_PDL: programmatic dependent launch between the per-step kernels of the latency path
   bool pdl_now = false;  // set while the latency path enqueues its chain
+  bool epi_colsum = true;   // UVA_EPI_COLSUM: bias gradients of mlp.0 / cond_embed reduced in the SiLU' GEMM epilogue (warp shuffles + atomics)
   bool fuse_colsum = true;  // UVA_FUSE_COLSUM: bias gradients of mlp.2 / gate modulation summed inside k_gate_bwd
   bool final_tc = true;  // UVA_FINAL_TC: final-layer backward (dgrad K = 32, wgrad M = 2C) on the tcgen05 GEMMs
   bool fuse_inproj = true;  // UVA_FUSE_INPROJ: input_proj + first LayerNorm-modulate in one kernel on the latency path
@@ -359,6 +360,7 @@ extern "C" int uva_head_create(const UvaHeadDesc* desc, UvaHead** out) {
   if (const char* e = getenv("UVA_FINAL_TC")) h->final_tc = atoi(e) != 0;
   if (const char* e = getenv("UVA_TRAIN_GRAPH")) h->train_graph = atoi(e) != 0;
   if (const char* e = getenv("UVA_FUSE_COLSUM")) h->fuse_colsum = atoi(e) != 0;
+  if (const char* e = getenv("UVA_EPI_COLSUM")) h->epi_colsum = atoi(e) != 0;
   if (const char* e = getenv("UVA_GRID_MULT")) { int v = atoi(e); if (v >= 1 && v <= 64) h->grid_mult = v; }
   CUDA_TRY(cudaStreamCreateWithFlags(&h->side, cudaStreamNonBlocking));
   CUDA_TRY(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
