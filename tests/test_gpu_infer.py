@@ -509,3 +509,31 @@ def test_error_paths(video):
     # empty batch is a no-op
     out = h2.sample(torch.zeros(0, 768, device=dev), torch.zeros(0, 16, device=dev), torch.zeros(100, 0, 16, device=dev))
     assert out.shape == (0, 16)
+
+
+@pytest.mark.parametrize("A", [6, 9, 10])
+@pytest.mark.parametrize("mode,tol_end", [(0, 1e-3), (1, 5e-2)])
+def test_other_channel_counts_vs_reference_golden(golden_dir, A, mode, tol_end):
+    """Action heads with act_dim = 10 (Libero / UMI / ToolHang) and the 6 / 9 channel proprioception heads
+    (MAR:298, 317, 332): the 16-row predict_action call (latency path in bf16 mode) and the same rows tiled to
+    1040 rows (tile path, ragged last panel) against the reference's chain (tests/golden/head_dims.npz)."""
+    dev = _cuda()
+    g = _load(golden_dir, "head_dims")
+    p = f"a{A}."
+    P = O.make_params(A, 768, 1024, 6, seed=20 + A)
+    h = _head(A, 768, 1024, 6, P, mode, dev)
+    states = _T(g[p + "s_states"])
+    teacher = torch.cat([_T(g[p + "s_x_init"])[None], states[:-1]], dim=0)
+    args = (_T(g[p + "s_z"], dev), _T(g[p + "s_x_init"], dev), _T(g[p + "s_noise"], dev))
+    _, tr = h.sample(*args, temperature=0.95, cfg=1.0, clip_denoised=True, teacher=teacher.to(dev), trace=True)
+    _assert_close(tr.cpu(), states, mode)
+    out = h.sample(*args, temperature=0.95, cfg=1.0, clip_denoised=True).cpu()
+    ref = _T(g[p + "s_final"])
+    assert float((out - ref).abs().max()) <= tol_end * max(1.0, float(ref.abs().max()))
+    # 65 copies of the 16 rows = 1040 rows: every copy must reproduce the chain
+    R = 65
+    big = (args[0].repeat(R, 1), args[1].repeat(R, 1), args[2].repeat(1, R, 1))
+    _, trb = h.sample(*big, temperature=0.95, cfg=1.0, clip_denoised=True, teacher=teacher.to(dev).repeat(1, R, 1), trace=True)
+    trb = trb.cpu().reshape(states.shape[0], R, 16, A)
+    for r in (0, 31, R - 1):
+        _assert_close(trb[:, r], states, mode)

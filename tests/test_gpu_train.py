@@ -369,3 +369,30 @@ def test_error_paths(video):
     rc = _lib.lib().uva_head_loss_fwd(h._h, None, z.data_ptr(), None, t.data_ptr(), x.data_ptr(), 4,
                                       loss.data_ptr(), None, ws.data_ptr(), ws.numel(), None)
     assert rc == -1
+
+
+@pytest.mark.parametrize("A", [6, 9, 10])
+@pytest.mark.parametrize("mode", [0, 1], ids=["fp32", "bf16"])
+def test_other_channel_counts_vs_reference_golden(golden_dir, A, mode):
+    """Training rows, d z and parameter gradients of the act_dim = 10 and the 6 / 9 channel heads (MAR:298, 317,
+    332) against the reference's training_losses + autograd (tests/golden/head_dims.npz); 24 rows, one with t = 0."""
+    dev = _cuda()
+    g = np.load(os.path.join(golden_dir, "head_dims.npz"))
+    p = f"a{A}."
+    P = O.make_params(A, 768, 1024, 6, seed=20 + A)
+    h, names = _head(A, 768, 1024, 6, P, mode, dev)
+    loss, rows, dz, grads = _run(h, names, P, dev, _T(g[p + "tr_target"]), _T(g[p + "tr_z"]), None, _T(g[p + "tr_t"]), _T(g[p + "tr_noise"]))
+    rt = 2e-4 if mode == 0 else 2e-2
+    np.testing.assert_allclose(rows.numpy(), g[p + "tr_rowloss"], rtol=rt, atol=rt * float(np.abs(g[p + "tr_rowloss"]).max()))
+    assert abs(float(loss) - float(g[p + "tr_loss"])) <= (FP32_TOL if mode == 0 else BF16_LOSS_TOL) * abs(float(g[p + "tr_loss"]))
+    _check(dz, _T(g[p + "tr_dz"]), mode, "dz")
+    for k in names:
+        dg = g[p + "tr_gdigest." + k]
+        f = grads[k].double().flatten()
+        tol = 2e-4 if mode == 0 else BF16_GRAD_L2
+        assert abs(float(f.norm()) - dg[2]) <= tol * max(dg[2], 1e-12), (k, float(f.norm()), dg[2])
+        samp = f[_T(g[p + "tr_gidx." + k])]
+        ref = _T(g[p + "tr_gsample." + k])
+        if float(ref.abs().max()) > 0:
+            err = float((samp - ref).norm() / ref.norm())
+            assert err <= (1e-3 if mode == 0 else 4 * BF16_GRAD_L2), (k, err)

@@ -172,3 +172,31 @@ def test_philox_known_answers_and_moments():
     assert abs(float(np.mean(x.astype(np.float64) ** 4)) - 3.0) < 0.1  # kurtosis of a normal
     assert abs(float(np.corrcoef(x[0], x[1])[0, 1])) < 1e-2  # steps are independent streams
     assert not np.array_equal(x[0], O.philox_normal(1234, 1, 0, 1 << 18, 1)[0])  # the call offset matters
+
+
+@pytest.mark.parametrize("A", [6, 9, 10])
+def test_other_channel_counts(golden_dir, A):
+    """Heads the reference builds with act_dim = 10 (Libero / UMI / ToolHang) and with 6 / 9 proprioception channels
+    (MAR:298, 317, 332): sampling chain with clip_denoised and the training rows + gradients, against
+    tests/golden/head_dims.npz (make_golden_dims.py)."""
+    g = _load(golden_dir, "head_dims")
+    p = f"a{A}."
+    Pn = O.make_params(A, 768, 1024, 6, seed=20 + A)
+    P = O.to_torch_params(Pn)
+    S = O.create_schedule("100")
+    states = _T(g[p + "s_states"])
+    teacher = torch.cat([_T(g[p + "s_x_init"])[None], states[:-1]], dim=0)
+    _, tr = O.sample_loop(P, S, _T(g[p + "s_z"]), _T(g[p + "s_x_init"]), _T(g[p + "s_noise"]), temperature=0.95, cfg=1.0,
+                          clip_denoised=True, trace=True, teacher=teacher)
+    np.testing.assert_allclose(tr.numpy(), states.numpy(), rtol=1e-4, atol=1e-5)
+    Pg = O.to_torch_params(Pn, requires_grad=True)
+    St = O.create_schedule("")
+    z = _T(g[p + "tr_z"]).requires_grad_(True)
+    loss = O.diffactloss_forward(Pg, St, _T(g[p + "tr_target"]), z, _T(g[p + "tr_t"]), _T(g[p + "tr_noise"]))
+    loss.backward()
+    assert loss.item() == pytest.approx(float(g[p + "tr_loss"]), rel=1e-5)
+    np.testing.assert_allclose(z.grad.numpy(), g[p + "tr_dz"], rtol=1e-3, atol=1e-7)
+    for k, q in Pg.items():
+        dg = g[p + "tr_gdigest." + k]
+        f = q.grad.double().flatten()
+        np.testing.assert_allclose(np.array([f.abs().sum().item(), f.norm().item()]), dg[1:], rtol=1e-4, err_msg=k)
