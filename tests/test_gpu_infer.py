@@ -537,3 +537,51 @@ def test_other_channel_counts_vs_reference_golden(golden_dir, A, mode, tol_end):
     trb = trb.cpu().reshape(states.shape[0], R, 16, A)
     for r in (0, 31, R - 1):
         _assert_close(trb[:, r], states, mode)
+
+
+def test_module_sample_follows_the_reference_rng_order(video):
+    """The drop-in modules' sample(): DiffLoss.sample(z, temperature, cfg) (DL:68-90: start noise from the CPU
+    generator, halves duplicated with CFG, then one CUDA randn per step inside p_sample, GD:431) and
+    DiffActLoss.sample (DAL:168-232: pre-net, clip_denoised=True).  Re-drawing the same numbers in the same order
+    and running the oracle on them must give the module's output (fp32 mode, 20-step respacing so that a
+    free-running chain stays comparable)."""
+    dev, _, P = video
+    from unified_video_action_b200 import DiffActLoss, DiffLoss
+
+    kw = dict(n_frames=4, language_emb_model=None, language_emb_model_type=None, precision="fp32")
+    head = DiffLoss(16, 768, 6, 1024, "20", **kw)
+    head.net.load_state_dict({k: _T(v) for k, v in P.items()})
+    head = head.to(dev)
+    Pt = O.to_torch_params(P)
+    S = O.create_schedule("20")
+    gen = torch.Generator().manual_seed(8)
+    for cfg, N in ((3.0, 24), (1.0, 13)):
+        z = torch.randn(N, 768, generator=gen)
+        torch.manual_seed(99)
+        out = head.sample(z.to(dev), temperature=0.95, cfg=cfg)
+        torch.manual_seed(99)
+        if cfg != 1.0:
+            half = torch.randn(N // 2, 16)
+            x0 = torch.cat([half, half], dim=0)
+        else:
+            x0 = torch.randn(N, 16)
+        nz = torch.stack([torch.randn(N, 16, device=dev) for _ in range(20)]).cpu()
+        ref = O.sample_loop(Pt, S, z, x0, nz, temperature=0.95, cfg=cfg, clip_denoised=False)
+        assert out.shape == (N, 16)
+        assert float((out.cpu() - ref).abs().max()) <= 2e-3 * float(ref.abs().max()), cfg
+
+    Pa = O.make_params(2, 768, 1024, 6, seed=2)
+    act = DiffActLoss(2, 768, 6, 1024, "20", act_diff_testing_steps="20", **kw)
+    act.net.load_state_dict({k: _T(v) for k, v in Pa.items()})
+    act = act.to(dev)
+    zb = torch.randn(2, 1024, 768, generator=gen).to(dev)
+    torch.manual_seed(5)
+    out = act.sample(zb, temperature=0.9, cfg=1.0)
+    assert out.shape == (2, 16, 2)
+    torch.manual_seed(5)
+    with torch.no_grad():
+        rows = act.prenet(zb).reshape(32, 768).cpu()
+    x0 = torch.randn(32, 2)
+    nz = torch.stack([torch.randn(32, 2, device=dev) for _ in range(20)]).cpu()
+    ref = O.sample_loop(O.to_torch_params(Pa), S, rows, x0, nz, temperature=0.9, cfg=1.0, clip_denoised=True)
+    assert float((out.reshape(32, 2).cpu() - ref).abs().max()) <= 2e-3 * max(1.0, float(ref.abs().max()))
