@@ -585,3 +585,47 @@ def test_module_sample_follows_the_reference_rng_order(video):
     nz = torch.stack([torch.randn(32, 2, device=dev) for _ in range(20)]).cpu()
     ref = O.sample_loop(O.to_torch_params(Pa), S, rows, x0, nz, temperature=0.9, cfg=1.0, clip_denoised=True)
     assert float((out.reshape(32, 2).cpu() - ref).abs().max()) <= 2e-3 * max(1.0, float(ref.abs().max()))
+
+
+def test_prenet_graph_replay_equals_eager(monkeypatch):
+    """DiffActLoss.sample can replay its pre-net from a CUDA graph for small batches: same rows as the eager pre-net,
+    in-place weight updates are seen, a moved parameter or another shape re-captures."""
+    dev = _cuda()
+    from unified_video_action_b200 import DiffActLoss
+    from unified_video_action_b200.diffusion_action_loss import _PRENET_GRAPHS
+
+    monkeypatch.setenv("UVA_PRENET_GRAPH", "1")  # opt-in switch
+    torch.manual_seed(3)
+    act = DiffActLoss(2, 768, 6, 1024, "100", n_frames=4, language_emb_model=None, language_emb_model_type=None).to(dev)
+    with torch.no_grad():
+        for p in act.parameters():
+            if float(p.abs().max()) == 0.0:
+                p.normal_(0.0, 0.02)  # the zero-initialised AdaLN / final layers would hide the conditioning
+    z1 = torch.randn(1, 1024, 768, device=dev)
+    z2 = torch.randn(1, 1024, 768, device=dev)
+    with torch.no_grad():
+        e1, e2 = act.prenet(z1).clone(), act.prenet(z2).clone()
+        r1 = act._prenet_replay(z1).clone()
+        r2 = act._prenet_replay(z2).clone()
+        assert id(act) in _PRENET_GRAPHS
+        graph0 = _PRENET_GRAPHS[id(act)][1]
+        assert float((r1 - e1).abs().max()) <= 1e-5 * float(e1.abs().max())
+        assert float((r2 - e2).abs().max()) <= 1e-5 * float(e2.abs().max())
+        act.refine[2].bias.add_(0.5)  # in place: same storage, the replay must see it
+        r3 = act._prenet_replay(z2).clone()
+        assert _PRENET_GRAPHS[id(act)][1] is graph0
+        assert float((r3 - (e2 + 0.5)).abs().max()) <= 1e-4
+        z3 = torch.randn(2, 1024, 768, device=dev)  # another shape re-captures
+        r4 = act._prenet_replay(z3).clone()
+        assert _PRENET_GRAPHS[id(act)][1] is not graph0
+        assert float((r4 - act.prenet(z3)).abs().max()) <= 1e-5 * float(r4.abs().max())
+        # whole call: graph on / off give the same actions (same RNG draws)
+        torch.manual_seed(11)
+        a_on = act.sample(z1, temperature=0.95, cfg=1.0)
+        monkeypatch.setenv("UVA_PRENET_GRAPH", "0")
+        torch.manual_seed(11)
+        a_off = act.sample(z1, temperature=0.95, cfg=1.0)
+    assert a_on.shape == (1, 16, 2)
+    assert float((a_on - a_off).abs().max()) <= 2e-2
+    with torch.enable_grad():  # training never takes the graph
+        assert act._prenet_replay(z1.requires_grad_(True)).requires_grad
