@@ -629,3 +629,28 @@ def test_prenet_graph_replay_equals_eager(monkeypatch):
     assert float((a_on - a_off).abs().max()) <= 2e-2
     with torch.enable_grad():  # training never takes the graph
         assert act._prenet_replay(z1.requires_grad_(True)).requires_grad
+
+
+@pytest.mark.parametrize("N,k_end", [(896, 12), (300, 7), (1024, 5), (129, 5)])
+def test_lnmod_prephase_equals_separate_launch(video, monkeypatch, N, k_end):
+    """Latency path between 129 and 1024 rows: the LayerNorm-modulate of blocks >= 1 runs as the pre-phase of
+    GEMM1 (the CTAs of a 128-row panel produce the A operand, meet at a panel barrier, then load it with TMA).
+    Same arithmetic as k_lnmod -> bit-identical to the path with the separate launch, call after call."""
+    dev, g, P = video
+    gen = torch.Generator().manual_seed(N)
+    z = torch.randn(N, 768, generator=gen).to(dev)
+    x0 = torch.randn(N, 16, generator=gen).to(dev)
+    nz = torch.randn(100, N, 16, generator=gen).to(dev)
+    outs, counts = {}, {}
+    for flag in ("0", "1"):
+        monkeypatch.setenv("UVA_FUSE_LNPRE", flag)
+        h = _head(16, 768, 1024, 6, P, 1, dev)
+        c0 = h.launch_count()
+        a = h.sample(z, x0, nz, temperature=0.95, cfg=1.0, k_begin=0, k_end=k_end).clone()
+        counts[flag] = h.launch_count() - c0
+        b = h.sample(z, x0, nz, temperature=0.95, cfg=1.0, k_begin=0, k_end=k_end).clone()  # graph replay
+        torch.cuda.synchronize()
+        assert torch.equal(a, b), flag
+        outs[flag] = a
+    assert torch.equal(outs["0"], outs["1"])
+    assert counts["1"] <= counts["0"] - 5 * k_end, counts

@@ -3,6 +3,7 @@
 // GD = diffusion/gaussian_diffusion.py).
 #pragma once
 #include "common.cuh"
+#include "lnmod_row.cuh"
 
 namespace uva {
 
@@ -277,66 +278,13 @@ __global__ void __launch_bounds__(256)
 k_lnmod(const float* __restrict__ h, const float* __restrict__ ln_w, const float* __restrict__ ln_b,
         const TA* __restrict__ shift, const TA* __restrict__ scale, int64_t ldmod,
         TA* __restrict__ a, float* __restrict__ stats, int64_t rows) {
-  constexpr int W = NV * 128;
   griddep_wait();
   griddep_launch();
   const int lane = threadIdx.x & 31;
   const int64_t warp_global = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int64_t warps_total = ((int64_t)gridDim.x * blockDim.x) >> 5;
-  for (int64_t r = warp_global; r < rows; r += warps_total) {
-    float4 v[NV];
-    float s = 0.f;
-#pragma unroll
-    for (int i = 0; i < NV; ++i) {
-      v[i] = *reinterpret_cast<const float4*>(h + r * W + (lane + 32 * i) * 4);
-      s += (v[i].x + v[i].y) + (v[i].z + v[i].w);
-    }
-    const float mean = warp_sum(s) * (1.0f / W);
-    float ss = 0.f;
-#pragma unroll
-    for (int i = 0; i < NV; ++i) {
-      const float dx = v[i].x - mean, dy = v[i].y - mean, dz = v[i].z - mean, dw = v[i].w - mean;
-      ss += (dx * dx + dy * dy) + (dz * dz + dw * dw);
-    }
-    const float rstd = rsqrtf(warp_sum(ss) * (1.0f / W) + 1e-6f);
-    if (stats && lane == 0) {
-      stats[2 * r] = mean;
-      stats[2 * r + 1] = rstd;
-    }
-#pragma unroll
-    for (int i = 0; i < NV; ++i) {
-      const int j = (lane + 32 * i) * 4;
-      float n[4] = {(v[i].x - mean) * rstd, (v[i].y - mean) * rstd, (v[i].z - mean) * rstd,
-                    (v[i].w - mean) * rstd};
-      if (ln_w) {
-        const float4 g = __ldg(reinterpret_cast<const float4*>(ln_w + j));
-        const float4 b = __ldg(reinterpret_cast<const float4*>(ln_b + j));
-        n[0] = n[0] * g.x + b.x; n[1] = n[1] * g.y + b.y; n[2] = n[2] * g.z + b.z; n[3] = n[3] * g.w + b.w;
-      }
-      float sh[4], sc[4];
-      if constexpr (sizeof(TA) == 2) {
-        const uint2 us = *reinterpret_cast<const uint2*>(shift + r * ldmod + j);
-        const uint2 uc = *reinterpret_cast<const uint2*>(scale + r * ldmod + j);
-        const __nv_bfloat162 s0 = *reinterpret_cast<const __nv_bfloat162*>(&us.x), s1 = *reinterpret_cast<const __nv_bfloat162*>(&us.y);
-        const __nv_bfloat162 c0 = *reinterpret_cast<const __nv_bfloat162*>(&uc.x), c1 = *reinterpret_cast<const __nv_bfloat162*>(&uc.y);
-        sh[0] = __low2float(s0); sh[1] = __high2float(s0); sh[2] = __low2float(s1); sh[3] = __high2float(s1);
-        sc[0] = __low2float(c0); sc[1] = __high2float(c0); sc[2] = __low2float(c1); sc[3] = __high2float(c1);
-      } else {
-        const float4 fs = *reinterpret_cast<const float4*>(shift + r * ldmod + j);
-        const float4 fc = *reinterpret_cast<const float4*>(scale + r * ldmod + j);
-        sh[0] = fs.x; sh[1] = fs.y; sh[2] = fs.z; sh[3] = fs.w;
-        sc[0] = fc.x; sc[1] = fc.y; sc[2] = fc.z; sc[3] = fc.w;
-      }
-      TA o[4];
-#pragma unroll
-      for (int q = 0; q < 4; ++q) o[q] = from_f32<TA>(n[q] * (1.0f + sc[q]) + sh[q]);
-      if constexpr (sizeof(TA) == 2) {
-        *reinterpret_cast<uint2*>(a + r * W + j) = *reinterpret_cast<uint2*>(o);
-      } else {
-        *reinterpret_cast<float4*>(a + r * W + j) = *reinterpret_cast<float4*>(o);
-      }
-    }
-  }
+  for (int64_t r = warp_global; r < rows; r += warps_total)
+    lnmod_row<TA, NV>(h, ln_w, ln_b, shift, scale, ldmod, a, stats, r, lane);
 }
 
 // Generic-width variant (W multiple of 32, any size; three passes through L1) for test geometries.

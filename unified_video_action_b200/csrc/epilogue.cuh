@@ -28,6 +28,18 @@ struct EpiArgs {
   // EPI_DSILU_ACT on the CTA-pair kernel: column sums of the fp32 result (the bias gradient of the Linear in front of
   // the SiLU) are reduced over each warp's 32 rows with shuffles and added here with one atomic per column; null: off
   float* colsum = nullptr;
+  // LayerNorm-modulate pre-phase of the latency-path GEMM1 (umma_gemm_tn_kernel<.., EPI_SILU_ACT>, one wave, K = 1024):
+  // before the main loop the CTAs of a 128-row panel produce the A operand a = LN(h) (1 + scale) + shift themselves
+  // (a few rows each), meet at a panel barrier (pre_bar: {count, generation} per panel) and only then start their TMA
+  // loads of A.  Replaces one k_lnmod launch per block and denoise step.  pre_h == null: off.
+  const float* pre_h = nullptr;      // [M, K] fp32 residual stream
+  const void* pre_shift = nullptr;   // TA, row stride pre_ldm
+  const void* pre_scale = nullptr;
+  int64_t pre_ldm = 0;
+  const float* pre_lnw = nullptr;    // LayerNorm affine or null
+  const float* pre_lnb = nullptr;
+  void* pre_a = nullptr;             // [M, K] TA: the tensor the A map points at
+  unsigned int* pre_bar = nullptr;   // [m_tiles][2], zero-initialised once, self-resetting
 };
 
 enum EpiKind {

@@ -17,6 +17,7 @@
 #pragma once
 #include "common.cuh"
 #include "epilogue.cuh"
+#include "lnmod_row.cuh"
 
 namespace uva {
 
@@ -237,6 +238,51 @@ umma_gemm_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   const uint32_t tmem_base = *tmem_slot;
   griddep_wait();    // (programmatic dependent launch: everything above overlapped the previous kernel's tail)
   griddep_launch();  // after the wait: triggering before it (next kernel two ahead) measured slower
+
+  if constexpr (KIND == EPI_SILU_ACT && !A_MN && sizeof(TA) == 2) {
+    if (ep.pre_h != nullptr) {
+      // LayerNorm-modulate pre-phase (see EpiArgs): the host guarantees gridDim.x == num_tiles (one tile per CTA, all
+      // CTAs co-resident), splits == 1 and K == 1024.  CTA n_blk of a panel takes rows n_blk * rp .. + rp of it.
+      int64_t m_blk; int n_blk;
+      ug_tile_coords((int64_t)blockIdx.x, m_tiles, n_tiles, gm, m_blk, n_blk);
+      const int rp = (UG_BM + n_tiles - 1) / n_tiles;
+      int64_t r1 = m_blk * UG_BM + (int64_t)(n_blk + 1) * rp;
+      if (r1 > (m_blk + 1) * UG_BM) r1 = (m_blk + 1) * UG_BM;
+      if (r1 > M) r1 = M;
+      for (int64_t r = m_blk * UG_BM + (int64_t)n_blk * rp + warp; r < r1; r += UG_THREADS / 32)
+        lnmod_row<TA, 8>(ep.pre_h, ep.pre_lnw, ep.pre_lnb, reinterpret_cast<const TA*>(ep.pre_shift),
+                         reinterpret_cast<const TA*>(ep.pre_scale), ep.pre_ldm, reinterpret_cast<TA*>(ep.pre_a), nullptr, r, lane);
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        // sense-reversing barrier of the n_tiles CTAs of this panel: the generation is read before arriving (it cannot
+        // change until this CTA has arrived), the count wraps to zero by itself -> nothing to reset between launches
+        unsigned int* cnt = ep.pre_bar + 2 * m_blk;
+        unsigned int* gen = cnt + 1;
+        unsigned int g0, g;
+        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(g0) : "l"(gen) : "memory");
+        // release: this CTA's rows of a (ordered before this thread by the bar.sync above) are visible before the arrival
+        unsigned int old;
+        asm volatile("atom.release.gpu.global.inc.u32 %0, [%1], %2;" : "=r"(old) : "l"(cnt), "r"((unsigned int)n_tiles - 1u) : "memory");
+        if (old == (unsigned int)n_tiles - 1u) {
+          asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(gen) : "memory");
+        } else {
+          uint32_t spins = 0;
+          uint64_t t0 = 0;
+          do {
+            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(g) : "l"(gen) : "memory");
+            if ((++spins & 0xFFFu) == 0) {  // a lost CTA becomes a trap instead of a hung GPU
+              const uint64_t now = global_timer_ns();
+              if (t0 == 0) t0 = now;
+              else if (now - t0 > 4000000000ull) __trap();
+            }
+          } while (g == g0);
+        }
+      }
+      __syncthreads();
+      // the other CTAs wrote a through the generic proxy; the TMA loads below read it through the async proxy
+      asm volatile("fence.proxy.async.global;" ::: "memory");
+    }
+  }
 
   if (warp == 0) {
     // ===================== TMA producer =====================

@@ -137,6 +137,7 @@ struct DevTables {  // fp32 device copies of one process' tables, [T] each
         *coef1 = nullptr, *coef2 = nullptr, *post_logvar = nullptr, *log_beta = nullptr;
 };
 
+static const int kLnPrePanels = 64;  // 128-row panels the LayerNorm pre-phase barriers cover (latency path: <= small_rows / 128)
 struct UvaHead {
   UvaHeadDesc d;
   int num_sms = 148;
@@ -191,6 +192,12 @@ struct UvaHead {
   bool fuse_ddpm = true;
   bool pdl = true;       // UVA_PDL: programmatic dependent launch between the per-step kernels of the latency path
   bool pdl_now = false;  // set while the latency path enqueues its chain
+  // UVA_FUSE_LNPRE=1: latency path, LayerNorm-modulate as the pre-phase of GEMM1 (umma_gemm.cuh).  Bit-identical and 5
+  // launches per step fewer, but measured slower on B200 (896 rows: 17.23 -> 17.52 ms per 100-step call): with
+  // programmatic dependent launch the separate k_lnmod costs only its own critical path, the pre-phase adds the
+  // panel barrier's two L2 round trips in front of the first TMA load -> off by default
+  bool fuse_lnpre = false;
+  unsigned int* lnpre_bar = nullptr;  // [kLnPrePanels][2] panel barriers of that pre-phase
   bool epi_colsum = true;   // UVA_EPI_COLSUM: bias gradients of mlp.0 / cond_embed reduced in the SiLU' GEMM epilogue (warp shuffles + atomics)
   bool fuse_colsum = true;  // UVA_FUSE_COLSUM: bias gradients of mlp.2 / gate modulation summed inside k_gate_bwd
   bool final_tc = true;  // UVA_FINAL_TC: final-layer backward (dgrad K = 32, wgrad M = 2C) on the tcgen05 GEMMs
@@ -361,6 +368,7 @@ extern "C" int uva_head_create(const UvaHeadDesc* desc, UvaHead** out) {
   if (const char* e = getenv("UVA_TRAIN_GRAPH")) h->train_graph = atoi(e) != 0;
   if (const char* e = getenv("UVA_FUSE_COLSUM")) h->fuse_colsum = atoi(e) != 0;
   if (const char* e = getenv("UVA_EPI_COLSUM")) h->epi_colsum = atoi(e) != 0;
+  if (const char* e = getenv("UVA_FUSE_LNPRE")) h->fuse_lnpre = atoi(e) != 0;
   if (const char* e = getenv("UVA_GRID_MULT")) { int v = atoi(e); if (v >= 1 && v <= 64) h->grid_mult = v; }
   CUDA_TRY(cudaStreamCreateWithFlags(&h->side, cudaStreamNonBlocking));
   CUDA_TRY(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
@@ -440,6 +448,8 @@ extern "C" int uva_head_create(const UvaHeadDesc* desc, UvaHead** out) {
     h->ob_adaw_p = take((size_t)h->nmod * W);
     h->ob_te2w = take(W * W);
     CUDA_TRY(cudaMalloc(&h->adab_p, (size_t)h->nmod * sizeof(float)));
+    CUDA_TRY(cudaMalloc(&h->lnpre_bar, (size_t)kLnPrePanels * 2 * sizeof(unsigned int)));
+    CUDA_TRY(cudaMemset(h->lnpre_bar, 0, (size_t)kLnPrePanels * 2 * sizeof(unsigned int)));
     for (int b = 0; b < d.depth; ++b) {
       h->ob_w1.push_back(take(W * W)); h->ob_w2.push_back(take(W * W));
     }
@@ -460,7 +470,7 @@ extern "C" void uva_head_destroy(UvaHead* h) {
   if (!h) return;
   cudaFree(h->d_tables); cudaFree(h->feat); cudaFree(h->temb); cudaFree(h->temb_hidden); cudaFree(h->temb_pre);
   cudaFree(h->temb_hidden_b); cudaFree(h->temb_pre_b); cudaFree(h->feat_b);
-  cudaFree(h->wf); cudaFree(h->wb); cudaFree(h->adab_p); cudaFree(h->d_tsteps); cudaFree(h->d_coef);
+  cudaFree(h->wf); cudaFree(h->wb); cudaFree(h->adab_p); cudaFree(h->d_tsteps); cudaFree(h->d_coef); cudaFree(h->lnpre_bar);
   for (auto& g : h->graphs)
     if (g.exec) cudaGraphExecDestroy(g.exec);
   for (auto& g : h->tgraphs)
