@@ -219,6 +219,13 @@ k_lnmod_bwd(const TA* __restrict__ da, const float* __restrict__ h, const float*
     const float mean = stats[2 * r], rstd = stats[2 * r + 1];
     float xh[NV][4], dx[NV][4];
     float s1 = 0.f, s2 = 0.f;
+    // the running d h is requested together with the other operands of the row: one memory round trip per row
+    // instead of two (8 warps per SM: the per-row latency chain is what bounds this kernel)
+    float4 prev[NV];
+    if (!first) {
+#pragma unroll
+      for (int i = 0; i < NV; ++i) prev[i] = *reinterpret_cast<const float4*>(dh + r * W + (lane + 32 * i) * 4);
+    }
 #pragma unroll
     for (int i = 0; i < NV; ++i) {
       const int j = (lane + 32 * i) * 4;
@@ -259,7 +266,7 @@ k_lnmod_bwd(const TA* __restrict__ da, const float* __restrict__ h, const float*
 #pragma unroll
       for (int q = 0; q < 4; ++q) o[q] = rstd * (dx[i][q] - s1 - xh[i][q] * s2);
       if (!first) {
-        const float4 p = *reinterpret_cast<const float4*>(dh + r * W + j);
+        const float4 p = prev[i];
         o[0] += p.x; o[1] += p.y; o[2] += p.z; o[3] += p.w;
       }
       store4(dh + r * W + j, o);
