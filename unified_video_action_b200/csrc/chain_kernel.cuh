@@ -156,12 +156,20 @@ __device__ __forceinline__ void ch_stage_lnmod(uint32_t* A, const float* h, int 
     const uint2* scp = reinterpret_cast<const uint2*>(scale + (int64_t)row * ldmod);
     float4 v[8];
     uint2 shv[8], scv[8];  // issued together with the h loads: one L2 round trip for the whole row
+    float4 gwv[8], gbv[8];  // ... and so is the LayerNorm affine (L1 is too small here to keep it across layers)
 #pragma unroll
     for (int i = 0; i < 8; ++i) v[i] = __ldcg(hp + i * 32 + lane);
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
       shv[i] = __ldg(shp + i * 32 + lane);
       scv[i] = __ldg(scp + i * 32 + lane);
+    }
+    if (ln_w != nullptr) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        gwv[i] = __ldg(reinterpret_cast<const float4*>(ln_w) + i * 32 + lane);
+        gbv[i] = __ldg(reinterpret_cast<const float4*>(ln_b) + i * 32 + lane);
+      }
     }
     float s = 0.f;
 #pragma unroll
@@ -179,8 +187,7 @@ __device__ __forceinline__ void ch_stage_lnmod(uint32_t* A, const float* h, int 
       const int e = i * 32 + lane;  // float4 index inside the row
       float n0 = (v[i].x - mean) * rstd, n1 = (v[i].y - mean) * rstd, n2 = (v[i].z - mean) * rstd, n3 = (v[i].w - mean) * rstd;
       if (ln_w != nullptr) {
-        const float4 gw = __ldg(reinterpret_cast<const float4*>(ln_w) + e);
-        const float4 gb = __ldg(reinterpret_cast<const float4*>(ln_b) + e);
+        const float4 gw = gwv[i], gb = gbv[i];
         n0 = fmaf(n0, gw.x, gb.x); n1 = fmaf(n1, gw.y, gb.y); n2 = fmaf(n2, gw.z, gb.z); n3 = fmaf(n3, gw.w, gb.w);
       }
       const uint2 sh = shv[i], sc = scv[i];
@@ -251,12 +258,20 @@ __device__ __forceinline__ void ch_stage_lnmod_cl(uint32_t* A, const float* h, i
   const uint2* scp = reinterpret_cast<const uint2*>(scale + (int64_t)row * ldmod);
   float4 v[8];
   uint2 shv[8], scv[8];
+  float4 gwv[8], gbv[8];
 #pragma unroll
   for (int i = 0; i < 8; ++i) v[i] = __ldcg(hp + i * 32 + lane);
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
     shv[i] = __ldg(shp + i * 32 + lane);
     scv[i] = __ldg(scp + i * 32 + lane);
+  }
+  if (ln_w != nullptr) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      gwv[i] = __ldg(reinterpret_cast<const float4*>(ln_w) + i * 32 + lane);
+      gbv[i] = __ldg(reinterpret_cast<const float4*>(ln_b) + i * 32 + lane);
+    }
   }
   float s = 0.f;
 #pragma unroll
@@ -274,8 +289,7 @@ __device__ __forceinline__ void ch_stage_lnmod_cl(uint32_t* A, const float* h, i
     const int e = i * 32 + lane;
     float n0 = (v[i].x - mean) * rstd, n1 = (v[i].y - mean) * rstd, n2 = (v[i].z - mean) * rstd, n3 = (v[i].w - mean) * rstd;
     if (ln_w != nullptr) {
-      const float4 gw = __ldg(reinterpret_cast<const float4*>(ln_w) + e);
-      const float4 gb = __ldg(reinterpret_cast<const float4*>(ln_b) + e);
+      const float4 gw = gwv[i], gb = gbv[i];
       n0 = fmaf(n0, gw.x, gb.x); n1 = fmaf(n1, gw.y, gb.y); n2 = fmaf(n2, gw.z, gb.z); n3 = fmaf(n3, gw.w, gb.w);
     }
     const uint2 sh = shv[i], sc = scv[i];
@@ -323,6 +337,20 @@ __global__ void __launch_bounds__(CH_THREADS, 1) k_denoise_chain(const __grid_co
   unsigned int epoch = 0;
   const uint32_t crank = (CL > 1) ? cluster_ctarank() : 0u;
 
+  // stationary small vectors: this CTA's 8 entries of every MLP bias and its 8 rows of input_proj (no global round
+  // trip in the epilogues: what bounds a layer is the number of dependent memory round trips, not bytes)
+  __shared__ float s_b[2 * CH_MAX_DEPTH][CH_F];
+  __shared__ float s_wi[CH_F][16];
+  __shared__ float s_bi[CH_F];
+  if (tid < 2 * p.depth * CH_F) {
+    const int l = tid >> 3, n = tid & 7;
+    s_b[l][n] = __ldg(((l & 1) ? p.b2[l >> 1] : p.b1[l >> 1]) + f0 + n);
+  }
+  if (tid < CH_F * 16) {
+    const int n = tid >> 4, c = tid & 15;
+    s_wi[n][c] = (c < C) ? __ldg(p.inp_w + (int64_t)(f0 + n) * C + c) : 0.f;
+    if (c == 0) s_bi[n] = __ldg(p.inp_b + f0 + n);
+  }
   // stationary weights: this CTA's 8 rows of every MLP matrix
   for (int l = 0; l < 2 * p.depth; ++l) {
     const bf16* src = ((l & 1) ? p.w2[l >> 1] : p.w1[l >> 1]) + (int64_t)f0 * W;
@@ -379,9 +407,8 @@ __global__ void __launch_bounds__(CH_THREADS, 1) k_denoise_chain(const __grid_co
       for (int it = tid; it < N * CH_F; it += CH_THREADS) {
         const int r = it >> 3, n = it & 7;
         const int rs = (p.half > 0 && r >= p.half) ? r - p.half : r;
-        const float* wi = p.inp_w + (int64_t)(f0 + n) * C;
-        float acc = __ldg(p.inp_b + f0 + n);
-        for (int c = 0; c < C; ++c) acc = fmaf(xs[rs * C + c], __ldg(wi + c), acc);
+        float acc = s_bi[n];
+        for (int c = 0; c < C; ++c) acc = fmaf(xs[rs * C + c], s_wi[n][c], acc);
         p.h[(int64_t)r * W + f0 + n] = acc;
       }
       chain_grid_sync(p.counter, epoch, p.dbg);
@@ -403,7 +430,7 @@ __global__ void __launch_bounds__(CH_THREADS, 1) k_denoise_chain(const __grid_co
         if (tid < CH_MT * CH_F) {
           const int rl = tid >> 3, n = tid & 7;
           if (m0 + rl < N) {
-            const float v = ch_reduced(red, tid) + __ldg(p.b1[b] + f0 + n);
+            const float v = ch_reduced(red, tid) + s_b[2 * b][n];
             p.u[(int64_t)(m0 + rl) * W + f0 + n] = __float2bfloat16_rn(silu_f(v));
           }
         }
@@ -414,6 +441,13 @@ __global__ void __launch_bounds__(CH_THREADS, 1) k_denoise_chain(const __grid_co
       // ---- GEMM2: h += gate * (u . W2^T + b2) (DL:167) ----
       for (int mt = 0; mt < mtiles; ++mt) {
         const int m0 = mt * CH_MT;
+        // the epilogue's own operands (gate from the modulation table, the residual element this thread wrote itself
+        // one block earlier) are requested before the staging, so they arrive under it
+        float gate = 0.f, hres = 0.f;
+        if (tid < CH_MT * CH_F && m0 + (tid >> 3) < N) {
+          gate = __bfloat162float(shift[(int64_t)(m0 + (tid >> 3)) * p.nmod + 2 * W + f0 + (tid & 7)]);
+          hres = __ldcg(p.h + (int64_t)(m0 + (tid >> 3)) * W + f0 + (tid & 7));
+        }
         if constexpr (CL > 1) {
           if (!(p.dbg & 2)) ch_stage_b16_cl<CL>(A, p.u, m0, N, tid, crank);
           cluster_sync_all();
@@ -425,10 +459,8 @@ __global__ void __launch_bounds__(CH_THREADS, 1) k_denoise_chain(const __grid_co
         if (tid < CH_MT * CH_F) {
           const int rl = tid >> 3, n = tid & 7;
           if (m0 + rl < N) {
-            const float v = ch_reduced(red, tid) + __ldg(p.b2[b] + f0 + n);
-            const float gate = __bfloat162float(shift[(int64_t)(m0 + rl) * p.nmod + 2 * W + f0 + n]);
-            float* hp = p.h + (int64_t)(m0 + rl) * W + f0 + n;
-            *hp = fmaf(gate, v, __ldcg(hp));
+            const float v = ch_reduced(red, tid) + s_b[2 * b + 1][n];
+            p.h[(int64_t)(m0 + rl) * W + f0 + n] = fmaf(gate, v, hres);
           }
         }
         if (CL > 1 && mt + 1 < mtiles) cluster_sync_all(); else __syncthreads();
