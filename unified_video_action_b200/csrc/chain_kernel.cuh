@@ -62,6 +62,7 @@ struct ChainArgs {
   int half;            // N / 2 with CFG, else 0
   float cfg, temperature;
   int clip;
+  int hold;  // cycles between a CTA's barrier arrival and its first poll (UVA_CHAIN_HOLD, default 480)
   int dbg;  // UVA_CHAIN_DBG (timing diagnosis only, results are wrong): 1 = no grid barriers, 2 = no activation staging
 };
 
@@ -74,7 +75,7 @@ __device__ __forceinline__ void mma_bf16_16816(float (&c)[4], uint32_t a0, uint3
 }
 
 // grid-wide barrier: every CTA arrives once per epoch on a monotonically increasing counter
-__device__ __forceinline__ void chain_grid_sync(unsigned int* counter, unsigned int& epoch, int dbg = 0) {
+__device__ __forceinline__ void chain_grid_sync(unsigned int* counter, unsigned int& epoch, int dbg = 0, int hold = 0) {
   if (dbg & 1) { __syncthreads(); return; }
   __syncthreads();
   if (threadIdx.x == 0) {
@@ -83,6 +84,13 @@ __device__ __forceinline__ void chain_grid_sync(unsigned int* counter, unsigned 
     // no separate fence: bar.sync orders the CTA's writes before this thread and the release is cumulative
     // (the pattern of CUTLASS' semaphore arrive); an extra MEMBAR.GPU cost 0.15 us per barrier
     asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(counter) : "memory");
+    if (hold > 0) {
+      // the first poll is held back: polls queue on the counter's L2 line in front of the arrivals of slower CTAs, and
+      // a poll issued before the barrier can possibly be complete only delays it (measured: flat optimum at 384 - 576 cycles,
+      // predict_action p50 5.72 -> 5.58 ms; 768 cycles is already later than the typical completion)
+      const long long t1 = clock64() + hold;
+      while (clock64() < t1) {}
+    }
     unsigned int v;
     uint32_t spins = 0;
     uint64_t t0 = 0;
@@ -411,7 +419,7 @@ __global__ void __launch_bounds__(CH_THREADS, 1) k_denoise_chain(const __grid_co
         for (int c = 0; c < C; ++c) acc = fmaf(xs[rs * C + c], s_wi[n][c], acc);
         p.h[(int64_t)r * W + f0 + n] = acc;
       }
-      chain_grid_sync(p.counter, epoch, p.dbg);
+      chain_grid_sync(p.counter, epoch, p.dbg, p.hold);
     }
     const bf16* modj = p.mod + (int64_t)j * N * p.nmod;
     for (int b = 0; b < p.depth; ++b) {
@@ -437,7 +445,7 @@ __global__ void __launch_bounds__(CH_THREADS, 1) k_denoise_chain(const __grid_co
         // the tile doubles as the reduction scratch: peers may only overwrite it once this CTA is done with it
         if (CL > 1 && mt + 1 < mtiles) cluster_sync_all(); else __syncthreads();
       }
-      chain_grid_sync(p.counter, epoch, p.dbg);
+      chain_grid_sync(p.counter, epoch, p.dbg, p.hold);
       // ---- GEMM2: h += gate * (u . W2^T + b2) (DL:167) ----
       for (int mt = 0; mt < mtiles; ++mt) {
         const int m0 = mt * CH_MT;
@@ -465,7 +473,7 @@ __global__ void __launch_bounds__(CH_THREADS, 1) k_denoise_chain(const __grid_co
         }
         if (CL > 1 && mt + 1 < mtiles) cluster_sync_all(); else __syncthreads();
       }
-      chain_grid_sync(p.counter, epoch, p.dbg);
+      chain_grid_sync(p.counter, epoch, p.dbg, p.hold);
     }
     // ---- final layer (DL:185-189): CTA o < 2C computes output column o ----
     if ((int)blockIdx.x < 2 * C) {
@@ -497,7 +505,7 @@ __global__ void __launch_bounds__(CH_THREADS, 1) k_denoise_chain(const __grid_co
         __syncwarp();
       }
     }
-    chain_grid_sync(p.counter, epoch, p.dbg);
+    chain_grid_sync(p.counter, epoch, p.dbg, p.hold);
   }
 }
 
