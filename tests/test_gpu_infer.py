@@ -251,7 +251,8 @@ def test_action_head_clip_chain(golden_dir, mode, tol_end):
     assert float((out - ref).abs().max()) <= tol_end * max(1.0, float(ref.abs().max()))
 
 
-@pytest.mark.parametrize("N,cfg,clip,k_end", [(16, 1.0, True, 100), (27, 1.0, True, 23), (112, 1.0, True, 23), (896, 1.0, False, 12), (32, 3.0, False, 30)])
+@pytest.mark.parametrize("N,cfg,clip,k_end", [(16, 1.0, True, 100), (27, 1.0, True, 23), (112, 1.0, True, 23), (896, 1.0, False, 12), (32, 3.0, False, 30),
+                                               (2048, 1.0, False, 6), (1536, 3.0, False, 6)])
 def test_latency_path_equals_chunked_path(video, monkeypatch, N, cfg, clip, k_end):
     """Small batches take the latency path (modulation tables of all steps hoisted into one GEMM; N <= 128:
     one persistent cooperative chain kernel, else the chain replayed from a CUDA graph): repeated calls
@@ -343,7 +344,7 @@ def test_cfg_with_identical_halves_equals_no_cfg(video):
     dev, g, P = video
     h = _head(16, 768, 1024, 6, P, 1, dev)
     gen = torch.Generator().manual_seed(29)
-    n, steps = 1200, 2  # both calls above the latency-path row limit: same kernels on both sides
+    n, steps = 2100, 2  # both calls above the latency-path row limit (2048): same kernels on both sides
     zc = torch.randn(n, 768, generator=gen).to(dev)
     x0 = torch.randn(n, 16, generator=gen).to(dev)
     nz = torch.randn(steps, n, 16, generator=gen).to(dev)

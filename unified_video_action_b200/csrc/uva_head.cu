@@ -207,7 +207,10 @@ struct UvaHead {
   // latency path (head_small.inc): small batches run with the AdaLN modulation of all denoise steps
   // computed up front and the whole chain replayed from a CUDA graph
   int* d_tsteps = nullptr;       // [T_gen] original-process timestep of loop iteration k
-  int64_t small_rows = 1024;     // UVA_SMALL_ROWS: largest batch that takes the latency path
+  // UVA_SMALL_ROWS: largest batch that takes the latency path.  Measured (100-step call, cfg 1): 1536 rows 35.8 -> 27.4 ms
+  // and 2048 rows 37.1 -> 29.6 ms against the chunked path (whose 256 x 256 pair tiles fill only 48 - 64 SMs there);
+  // even at 3072 rows, 4 % slower at 4096.  The modulation table of all steps costs 4.1 MB per row (8.4 GB at 2048).
+  int64_t small_rows = 2048;
   StepCoef* d_coef = nullptr;    // [T_gen] DDPM update coefficients of the sampling process, by timestep index
   bool use_chain = true;         // UVA_CHAIN: persistent chain kernel (chain_kernel.cuh)
   int64_t chain_rows = 32;       // UVA_CHAIN_ROWS: largest batch it takes (its time grows with rows / 16)
