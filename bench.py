@@ -252,12 +252,17 @@ def measure_train(dev, world, B=16, iters=5, warmup=2):
         dist.barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     marks = [torch.cuda.Event(enable_timing=True) for _ in range(iters)]
+    import gc
+
+    gc.collect()
+    gc.disable()  # a cyclic-GC pass of the host interpreter inside the timed region showed up as single 20 ms steps
     e0.record()
     for i in range(iters):
         loss = step()
         marks[i].record()
     e1.record()
     torch.cuda.synchronize()
+    gc.enable()
     ms = e0.elapsed_time(e1) / iters  # the reported number: whole timed region / steps
     per = sorted(a.elapsed_time(b) for a, b in zip([e0] + marks[:-1], marks))  # spread of the single steps
     rows = B * 1024 + B * 16
