@@ -129,6 +129,8 @@ umma_gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   cluster_sync_all();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  griddep_wait();    // programmatic dependent launch (when the launch asks for it): the prologue above overlapped the
+  griddep_launch();  // previous kernel's tail; no global memory is touched before this point
 
   if (warp == 0) {
     // ===================== TMA producer (both CTAs) =====================

@@ -191,6 +191,8 @@ struct UvaHead {
   } fin;
   bool fuse_ddpm = true;
   bool pdl = true;       // UVA_PDL: programmatic dependent launch between the per-step kernels of the latency path
+  bool pdl_big = true;   // UVA_PDL_BIG: programmatic dependent launch between the GEMMs of the chunked (throughput) path as well
+  bool pdl_train = false;  // UVA_PDL_TRAIN
   bool pdl_now = false;  // set while the latency path enqueues its chain
   // UVA_FUSE_LNPRE=1: latency path, LayerNorm-modulate as the pre-phase of GEMM1 (umma_gemm.cuh).  Bit-identical and 5
   // launches per step fewer, but measured slower on B200 (896 rows: 17.23 -> 17.52 ms per 100-step call): with
@@ -371,6 +373,8 @@ extern "C" int uva_head_create(const UvaHeadDesc* desc, UvaHead** out) {
   if (const char* e = getenv("UVA_TRAIN_GRAPH")) h->train_graph = atoi(e) != 0;
   if (const char* e = getenv("UVA_FUSE_COLSUM")) h->fuse_colsum = atoi(e) != 0;
   if (const char* e = getenv("UVA_EPI_COLSUM")) h->epi_colsum = atoi(e) != 0;
+  if (const char* e = getenv("UVA_PDL_BIG")) h->pdl_big = atoi(e) != 0;
+  if (const char* e = getenv("UVA_PDL_TRAIN")) h->pdl_train = atoi(e) != 0;
   if (const char* e = getenv("UVA_FUSE_LNPRE")) h->fuse_lnpre = atoi(e) != 0;
   if (const char* e = getenv("UVA_GRID_MULT")) { int v = atoi(e); if (v >= 1 && v <= 64) h->grid_mult = v; }
   CUDA_TRY(cudaStreamCreateWithFlags(&h->side, cudaStreamNonBlocking));
