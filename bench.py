@@ -242,10 +242,11 @@ def measure_train(dev, world, B=16, iters=5, warmup=2):
             allreduce_head_grads([vid, act])
         return loss
 
-    # at least 10 untimed steps: on a fresh box single steps up to the ~8th have been seen to stall for > 100 ms
-    # (lazy module loads of cuDNN / the allocator settling on its blocks, after which the graph replay of the small
-    # head starts); p50_ms / max_ms below show the spread of the timed steps
-    for _ in range(max(warmup, 10)):
+    # at least 30 untimed steps: the small head's fwd / bwd replay from CUDA graphs that the library captures the second
+    # time it sees a set of buffer pointers, and the caching allocator cycles through a few sets before it settles; a
+    # capture inside the timed region is a single 20 - 170 ms step (seen up to the ~15th step of a fresh process).
+    # p50_ms / max_ms below show the spread of the timed steps
+    for _ in range(max(warmup, 30)):
         step()
     torch.cuda.synchronize()
     if world > 1:
