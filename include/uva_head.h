@@ -169,12 +169,15 @@ int uva_adamw_ema_step(int32_t n_tensors, float* const* params, const float* con
  *   uva_nccl_unique_id  : rank 0 fills 128 bytes (host) that the caller broadcasts to the other ranks
  *                         (any out-of-band channel: torch.distributed store, MPI, a file);
  *   uva_nccl_comm_create: collective over all ranks; the current CUDA device is the rank's GPU;
- *   uva_head_allreduce_grads: flat = device pointer to `count` fp32 values, reduced in place. */
+ *   uva_head_allreduce_grads: flat = device pointer to `count` fp32 values, reduced in place;
+ *   uva_head_allreduce_grads_bf16: the same buffer crosses the link as bf16 (half the bytes): rounded into
+ *                         `scratch` (device, count * 2 bytes), reduced there by NCCL, widened back into flat. */
 int32_t uva_nccl_version(void);
 int uva_nccl_unique_id(void* out128 /*host*/);
 int uva_nccl_comm_create(int32_t world_size, int32_t rank, const void* id128 /*host*/, void** comm /*host*/);
 int uva_nccl_comm_destroy(void* comm);
 int uva_head_allreduce_grads(void* comm, float* flat, int64_t count, int32_t average, void* stream);
+int uva_head_allreduce_grads_bf16(void* comm, float* flat, void* scratch, int64_t count, int32_t average, void* stream);
 
 /* Joint training step (MAR:770-784): the video head (16 384 rows) and the action head (256 rows) are independent
  * and run on two streams.  The video head's persistent GEMM grids would take every SM, so the small head could

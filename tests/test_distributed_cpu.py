@@ -98,3 +98,87 @@ def test_gloo_world2_allreduce_and_sharding(tmp_path):
     mp.spawn(_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
     for r in range(world):
         assert (tmp_path / f"ok{r}").exists()
+
+
+class _FlatGrads(torch.autograd.Function):
+    """Stand-in for ``_FusedLoss`` on CPU: hands out views of ONE flat buffer as the parameter gradients and arms
+    the head's ``_GradSync`` exactly like ``_FusedLoss.backward`` does (the arithmetic of the real head needs a
+    B200; the early all-reduce logic only sees the flat buffer and the autograd hooks)."""
+
+    @staticmethod
+    def forward(ctx, net, scale, *params):
+        ctx.net, ctx.scale = net, scale
+        return sum((p.detach() * p.detach()).sum() for p in params) * 0 + torch.tensor(1.0)
+
+    @staticmethod
+    def backward(ctx, dloss):
+        from unified_video_action_b200.diffusion_loss import _grad_buffers
+
+        params = list(ctx.net.parameters())
+        flat, grads = _grad_buffers(params, torch.device("cpu"))
+        for g, p in zip(grads, params):
+            g.copy_(ctx.scale * torch.ones_like(p))
+        sync = getattr(ctx.net, "_grad_sync", None)
+        if sync is not None:
+            sync.arm(flat, params)
+        return (None, None, *grads)
+
+
+def _accum_worker(rank, world, port, out_dir):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from unified_video_action_b200 import allreduce_head_grads, overlap_allreduce
+
+        class Head(torch.nn.Module):
+            def __init__(self):
+                super().__init__()
+                self.net = torch.nn.Sequential(torch.nn.Linear(5, 7), torch.nn.Linear(7, 3))
+
+        head = Head()
+        overlap_allreduce([head])
+        sync = head.net._grad_sync
+        mean = sum(r + 1.0 for r in range(world)) / world
+
+        def backward(scale):
+            _FlatGrads.apply(head.net, scale, *head.net.parameters()).backward()
+
+        # 1. one backward: autograd adopts the views, the hooks start the collective, the consumer only waits
+        backward(rank + 1.0)
+        assert sync.pending is not None and sync.armed is None
+        assert allreduce_head_grads([head]) == 1
+        for p in head.net.parameters():
+            torch.testing.assert_close(p.grad, torch.full_like(p, mean))
+        # 2. gradient accumulation (ADVICE r1): two backwards before ONE allreduce_head_grads.  The first
+        # micro-step's early collective must be waited for and dropped, the accumulated sum reduced in full.
+        for p in head.net.parameters():
+            p.grad = None
+        backward(rank + 1.0)
+        assert sync.pending is not None
+        backward(10.0 * (rank + 1.0))
+        assert sync.pending is None, "the stale collective of micro-step 1 must not survive micro-step 2"
+        assert allreduce_head_grads([head]) == 1
+        for p in head.net.parameters():
+            torch.testing.assert_close(p.grad, torch.full_like(p, 11.0 * mean))
+        # 3. autograd clones instead of adopting (a tensor hook on one parameter): no early collective, plain reduce
+        for p in head.net.parameters():
+            p.grad = None
+        hd = head.net[0].weight.register_hook(lambda g: g * 1.0)
+        backward(rank + 1.0)
+        hd.remove()
+        assert sync.pending is None
+        assert allreduce_head_grads([head]) >= 1
+        for p in head.net.parameters():
+            torch.testing.assert_close(p.grad, torch.full_like(p, mean))
+        open(os.path.join(out_dir, f"ok{rank}"), "w").write("ok")
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.timeout(300)
+def test_gloo_world2_early_allreduce_under_gradient_accumulation(tmp_path):
+    world = 2
+    mp.spawn(_accum_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    for r in range(world):
+        assert (tmp_path / f"ok{r}").exists()

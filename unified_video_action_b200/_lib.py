@@ -48,7 +48,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
         return LIB_PATH
     nvcc = os.environ.get("NVCC", "nvcc")
     tmp = LIB_PATH + ".tmp.%d" % os.getpid()
-    cmd = [nvcc] + NVCC_FLAGS + ["-o", tmp, os.path.join(CSRC, "uva_head.cu")]
+    extra = os.environ.get("NVCC_EXTRA", "").split()  # e.g. -DUVA_DEBUG for the time-attribution switches
+    cmd = [nvcc] + NVCC_FLAGS + extra + ["-o", tmp, os.path.join(CSRC, "uva_head.cu")]
     if verbose:
         cmd.insert(1, "-Xptxas=-v")
     res = subprocess.run(cmd, capture_output=True, text=True)
@@ -74,7 +75,7 @@ SYMBOLS = [
     "uva_head_sample", "uva_head_loss_fwd", "uva_head_loss_bwd", "uva_head_launch_count",
     "uva_gemm_bf16_selftest", "uva_last_error", "uva_build_info", "uva_head_timing_enable", "uva_head_timing_read",
     "uva_adamw_ema_step", "uva_nccl_version", "uva_nccl_unique_id", "uva_nccl_comm_create", "uva_nccl_comm_destroy",
-    "uva_head_allreduce_grads", "uva_head_set_noise_seed", "uva_philox_normal", "uva_head_set_train_reserve",
+    "uva_head_allreduce_grads", "uva_head_allreduce_grads_bf16", "uva_head_set_noise_seed", "uva_philox_normal", "uva_head_set_train_reserve",
 ]
 
 
@@ -135,6 +136,8 @@ def lib() -> ctypes.CDLL:
         L.uva_nccl_comm_destroy.argtypes = [vp]
         L.uva_head_allreduce_grads.restype = ctypes.c_int
         L.uva_head_allreduce_grads.argtypes = [vp, vp, i64, i32, vp]
+        L.uva_head_allreduce_grads_bf16.restype = ctypes.c_int
+        L.uva_head_allreduce_grads_bf16.argtypes = [vp, vp, vp, i64, i32, vp]
         L.uva_last_error.restype = ctypes.c_char_p
         L.uva_build_info.restype = ctypes.c_char_p
         _lib = L
@@ -186,6 +189,8 @@ class Head:
         self._h = h
         self.device = torch.device("cuda", torch.cuda.current_device())
         self._ws: Dict[int, torch.Tensor] = {}
+        self._ws_streams: Dict[int, dict] = {}
+        self.fwd_gen = 0  # bumped by every loss_fwd: whose activations the training workspace holds
         self.n_params = lib().uva_head_num_params(depth)
 
     def __del__(self):
@@ -198,12 +203,26 @@ class Head:
 
     # ---- plumbing -------------------------------------------------------------------------
     def workspace(self, rows: int, what: int) -> torch.Tensor:
+        """Cached per-kind workspace.  A Head is single-stream and single-thread per call (like the reference
+        modules), but successive calls may come from different streams (the action head's side stream, the eager
+        backward stream) and the library's own second lane reads the buffer too: before a buffer is dropped for a
+        larger one, every stream that used it is recorded on it so that the caching allocator does not hand the
+        block out while kernels of those streams are still running."""
         need = int(lib().uva_head_workspace_bytes(self._h, rows, what))
         ws = self._ws.get(what)
+        cur = torch.cuda.current_stream(self.device)
+        users = self._ws_streams.setdefault(what, {})
         if ws is None or ws.numel() < need:
+            if ws is not None:
+                for st in users.values():
+                    ws.record_stream(st)
+                # the handle's internal lane stream is not a torch stream: drain it before the block can be reused
+                torch.cuda.synchronize(self.device)
+            users.clear()
             self._ws[what] = None
             ws = torch.empty(max(need, 1024), dtype=torch.uint8, device=self.device)
             self._ws[what] = ws
+        users[cur.cuda_stream] = cur
         return ws
 
     def set_train_reserve(self, sms: int) -> None:
@@ -279,6 +298,7 @@ class Head:
         loss = torch.empty(1, dtype=torch.float32, device=z.device)
         rows = torch.empty(N, dtype=torch.float32, device=z.device) if want_rows else None
         ws = self.workspace(N, 1)
+        self.fwd_gen += 1
         _check(lib().uva_head_loss_fwd(self._h, target.data_ptr(), z.data_ptr(), _ptr(mask), t.data_ptr(),
                                        noise.data_ptr(), N, loss.data_ptr(), _ptr(rows), ws.data_ptr(), ws.numel(),
                                        _stream()), "uva_head_loss_fwd")
@@ -334,7 +354,7 @@ class GradComm:
         self._c = c
         self.device = torch.device("cuda", torch.cuda.current_device())
 
-    def all_reduce_async(self, flat: torch.Tensor, average: bool = True) -> "torch.cuda.Event":
+    def all_reduce_async(self, flat: torch.Tensor, average: bool = True, bf16: bool = False) -> "torch.cuda.Event":
         """The same collective on this communicator's own stream, behind everything already enqueued on the
         caller's stream; returns the event a consumer of ``flat`` has to wait for.  All collectives of one
         communicator go through this one stream, so they keep one order on every rank."""
@@ -343,13 +363,21 @@ class GradComm:
             self._stream = torch.cuda.Stream(device=dev, priority=-1)
         self._stream.wait_event(torch.cuda.current_stream(dev).record_event())
         with torch.cuda.stream(self._stream):
-            self.all_reduce_(flat, average)
+            self.all_reduce_(flat, average, bf16=bf16)
         flat.record_stream(self._stream)
         return self._stream.record_event()
 
-    def all_reduce_(self, flat: torch.Tensor, average: bool = True) -> torch.Tensor:
+    def all_reduce_(self, flat: torch.Tensor, average: bool = True, bf16: bool = False) -> torch.Tensor:
+        """In-place all-reduce of a flat fp32 buffer on the current stream.  ``bf16``: the values cross NVLink as
+        bf16 (half the bytes; rounded into a scratch buffer, reduced there, widened back)."""
         if not flat.is_cuda or flat.dtype != torch.float32 or not flat.is_contiguous():
             raise RuntimeError("GradComm.all_reduce_: expected a contiguous fp32 CUDA tensor")
+        if bf16:
+            scratch = torch.empty(flat.numel(), dtype=torch.bfloat16, device=flat.device)
+            with torch.cuda.device(flat.device):
+                _check(lib().uva_head_allreduce_grads_bf16(self._c, flat.data_ptr(), scratch.data_ptr(), flat.numel(),
+                                                           int(average), _stream()), "uva_head_allreduce_grads_bf16")
+            return flat
         with torch.cuda.device(flat.device):
             _check(lib().uva_head_allreduce_grads(self._c, flat.data_ptr(), flat.numel(), int(average), _stream()),
                    "uva_head_allreduce_grads")

@@ -205,7 +205,7 @@ struct UvaHead {
   bool final_tc = true;  // UVA_FINAL_TC: final-layer backward (dgrad K = 32, wgrad M = 2C) on the tcgen05 GEMMs
   bool fuse_inproj = true;  // UVA_FUSE_INPROJ: input_proj + first LayerNorm-modulate in one kernel on the latency path
   PhiloxSeed noise{0, 0, 0, 0};  // uva_head_set_noise_seed: generator of the sampler's noise when step_noise == NULL
-  int dbg_skip = 0;  // UVA_DEBUG_SKIP (timing diagnosis only, results are wrong): 1 = no GEMM launches, 2 = no row kernels
+  int dbg_skip = 0;  // -DUVA_DEBUG builds only: UVA_DEBUG_SKIP (timing diagnosis, results are wrong): 1 = no GEMM launches, 2 = no row kernels
   // latency path (head_small.inc): small batches run with the AdaLN modulation of all denoise steps
   // computed up front and the whole chain replayed from a CUDA graph
   int* d_tsteps = nullptr;       // [T_gen] original-process timestep of loop iteration k
@@ -360,7 +360,9 @@ extern "C" int uva_head_create(const UvaHeadDesc* desc, UvaHead** out) {
   if (const char* e = getenv("UVA_PAIR")) h->pair = atoi(e) != 0;
   if (const char* e = getenv("UVA_QUAD")) h->quad = atoi(e) != 0;
   if (const char* e = getenv("UVA_FUSE_LN")) h->fuse_ln = atoi(e) != 0;
+#ifdef UVA_DEBUG  // result-corrupting timing switches exist only in a -DUVA_DEBUG build, never in the shipped library
   if (const char* e = getenv("UVA_DEBUG_SKIP")) h->dbg_skip = atoi(e);
+#endif
   if (const char* e = getenv("UVA_SMALL_ROWS")) h->small_rows = atol(e);
   if (const char* e = getenv("UVA_GRAPH")) h->use_graph = atoi(e) != 0;
   if (const char* e = getenv("UVA_CHAIN")) h->use_chain = atoi(e) != 0;

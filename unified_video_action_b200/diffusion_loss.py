@@ -224,6 +224,9 @@ class _FusedLoss(torch.autograd.Function):
     def forward(ctx, net: SimpleMLPAdaLN, target, z, mask, t, noise, *params):
         head = net.head()
         loss = head.loss_fwd(target, z, mask, t, noise)
+        # the activations the backward needs live in the head's one cached training workspace: remember which
+        # forward wrote them last (two forwards before a backward, or an eval forward in between)
+        ctx.fwd_gen = head.fwd_gen
         ctx.net = net
         ctx.has_mask = mask is not None
         ctx.z_dtype = z.dtype
@@ -267,15 +270,21 @@ class _FusedLoss(torch.autograd.Function):
                 raise RuntimeError("DiffLoss: backward through an eagerly differentiated loss can run only once")
             target, z, mask, t, noise = ctx.saved_tensors
             head = net.head()
+            if head.fwd_gen != ctx.fwd_gen:
+                # another forward went through this head since ours (e.g. (l1 + l2).backward(), an eval forward
+                # between forward and backward, a re-packed head): the workspace no longer holds our activations.
+                # Recompute them from the saved inputs - same draws, same arithmetic, so the same gradients as
+                # the reference's autograd gives - instead of differentiating the wrong forward.
+                head.loss_fwd(target, z, mask if ctx.has_mask else None, t, noise)
             flat, grads = _grad_buffers(params, z.device)
             dz = head.loss_bwd(dloss.float(), target, z, mask if ctx.has_mask else None, t, noise, grads)
         sync = getattr(net, "_grad_sync", None)
         if sync is not None:
             # data-parallel training (patch.overlap_allreduce): the head's gradients are complete here, long before
-            # the backbone's backward is; start their all-reduce now on the communicator's stream.  Only when
-            # autograd will adopt `flat` as the .grad storage (no gradient accumulation into existing .grad).
-            if all(p.grad is None for p in params if p.requires_grad):
-                sync.launch(flat)
+            # the backbone's backward is.  The collective starts from the parameters' post-accumulate-grad hooks once
+            # autograd has adopted the views of `flat` as .grad (see patch._GradSync); a collective of an earlier,
+            # unconsumed backward (gradient accumulation) is waited for here, before autograd adds into its buffer.
+            sync.arm(flat, params)
         return (None, None, dz.to(ctx.z_dtype) if ctx.needs_input_grad[2] else None, None, None, None, *grads)
 
 

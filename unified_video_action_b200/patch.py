@@ -86,7 +86,7 @@ def _shared_flat(grads):
 _COMMS: dict = {}  # id(process group) -> _lib.GradComm (NCCL communicator created through the C ABI)
 
 
-def _reduce_flat(flat: torch.Tensor, group, average: bool, world: int) -> None:
+def _reduce_flat(flat: torch.Tensor, group, average: bool, world: int, bf16: bool = False) -> None:
     """One in-place all-reduce of a flat fp32 buffer.  CUDA buffers go through the library
     (``uva_head_allreduce_grads`` = ncclAllReduce with ncclAvg on the caller's stream); host buffers exist
     only in the CPU tests of this host logic and use the torch.distributed group (gloo) directly."""
@@ -101,22 +101,48 @@ def _reduce_flat(flat: torch.Tensor, group, average: bool, world: int) -> None:
             comm = _COMMS[key] = _lib.GradComm(group)
         if getattr(comm, "_stream", None) is not None:
             # this communicator already runs collectives on its own stream (overlap_allreduce): keep them all there
-            torch.cuda.current_stream(flat.device).wait_event(comm.all_reduce_async(flat, average))
+            torch.cuda.current_stream(flat.device).wait_event(comm.all_reduce_async(flat, average, bf16=bf16))
         else:
-            comm.all_reduce_(flat, average)
+            comm.all_reduce_(flat, average, bf16=bf16)
         return
     dist.all_reduce(flat, group=group)
     if average:
         flat /= world
 
 
-class _GradSync:
-    """Per-head state of the early all-reduce: (flat gradient buffer, completion event) of the collective
-    that ``_FusedLoss.backward`` started."""
+class _Done:
+    """Completion of one early collective: a CUDA event of the communicator's stream (NCCL through the C ABI) or
+    a torch.distributed work handle (gloo, the CPU tests of this host logic)."""
 
-    def __init__(self, group, average: bool):
-        self.group, self.average = group, average
-        self.pending = None
+    def __init__(self, event=None, work=None):
+        self.event, self.work = event, work
+
+    def wait(self, device) -> None:
+        if self.event is not None:
+            torch.cuda.current_stream(device).wait_event(self.event)
+        if self.work is not None:
+            self.work.wait()
+
+
+class _GradSync:
+    """Per-head state of the early all-reduce (``overlap_allreduce``).
+
+    ``_FusedLoss.backward`` only ARMS it with the flat buffer whose views it returns as gradients; the collective
+    itself is launched from the parameters' post-accumulate-grad hooks, when the last of them has fired and every
+    ``p.grad`` really is a view of that buffer (autograd adopted the views).  If autograd cloned instead (hooks,
+    ``create_graph``, a layout mismatch) or accumulated into an existing ``.grad`` (gradient accumulation), nothing
+    is launched and ``allreduce_head_grads`` does the plain reduce.  A collective of an EARLIER backward that
+    nobody consumed yet (second micro-step of an accumulation) is waited for in ``arm`` - before autograd adds the
+    new gradients into the buffer that collective is still rewriting - and forgotten, so that
+    ``allreduce_head_grads`` reduces the accumulated sum in full."""
+
+    def __init__(self, group, average: bool, bf16: bool = False):
+        self.group, self.average, self.bf16 = group, average, bf16
+        self.pending = None   # (flat, _Done) of the collective in flight
+        self.armed = None     # flat buffer of the backward whose AccumulateGrad nodes are running now
+        self.count = self.need = 0
+        self.params = ()
+        self.handles = []
 
     def comm(self, device):
         from . import _lib
@@ -127,27 +153,61 @@ class _GradSync:
             c = _COMMS[key] = _lib.GradComm(self.group)
         return c
 
+    def arm(self, flat: torch.Tensor, params) -> None:
+        if self.pending is not None:
+            self.pending[1].wait(flat.device)
+            self.pending = None
+        self.armed, self.count, self.params = flat, 0, params
+        self.need = sum(1 for p in params if p.requires_grad)
+
+    def hook(self, _param) -> None:
+        if self.armed is None:
+            return
+        self.count += 1
+        if self.count < self.need:
+            return
+        flat, self.armed = self.armed, None
+        sp = flat.untyped_storage().data_ptr()
+        if all(p.grad is not None and p.grad.untyped_storage().data_ptr() == sp for p in self.params if p.requires_grad):
+            self.launch(flat)
+
     def launch(self, flat: torch.Tensor) -> None:
-        self.pending = (flat, self.comm(flat.device).all_reduce_async(flat, self.average))
+        if flat.is_cuda:
+            self.pending = (flat, _Done(event=self.comm(flat.device).all_reduce_async(flat, self.average, bf16=self.bf16)))
+            return
+        import torch.distributed as dist
+
+        if self.average:
+            flat /= dist.get_world_size(self.group)
+        self.pending = (flat, _Done(work=dist.all_reduce(flat, group=self.group, async_op=True)))
 
 
-def overlap_allreduce(heads: Iterable[nn.Module], group=None, average: bool = True) -> None:
-    """Start each head's gradient all-reduce from inside its backward ("issued from the extension
-    when the last wgrad tile lands, overlapped with the backbone's backward"): the fused backward of a head ends
-    long before the MAR decoder / encoder backward does, so the collective runs on the communicator's own stream
-    beside it.  ``allreduce_head_grads`` afterwards only waits for those collectives (and reduces what else the
-    head owns, e.g. the PyTorch pre-net).  Needs the NCCL process group to be initialised; ``None`` heads or
-    ``heads=[]`` are fine.  Call once after ``patch()``."""
+def overlap_allreduce(heads: Iterable[nn.Module], group=None, average: bool = True, bf16: bool = False) -> None:
+    """Start each head's gradient all-reduce as soon as its gradients are in place ("issued from the
+    extension when the last wgrad tile lands, overlapped with the backbone's backward"): the fused backward of a
+    head ends long before the MAR decoder / encoder backward does, so the collective runs on the communicator's own
+    stream beside it.  ``allreduce_head_grads`` afterwards only waits for those collectives (and reduces what else
+    the head owns, e.g. the PyTorch pre-net).  ``bf16``: the flat buffer crosses NVLink as bf16 (71.5 MB per head
+    instead of 143 MB; converted on both sides by the library).  Needs the process group to be initialised;
+    ``None`` heads or ``heads=[]`` are fine.  Call once after ``patch()``; calling it again replaces the hooks."""
     for head in heads:
         net = getattr(head, "net", None)
-        if net is not None:
-            net._grad_sync = _GradSync(group, average)
+        if net is None:
+            continue
+        old = getattr(net, "_grad_sync", None)
+        if old is not None:
+            for hd in old.handles:
+                hd.remove()
+        sync = net._grad_sync = _GradSync(group, average, bf16)
+        for p in net.parameters():
+            sync.handles.append(p.register_post_accumulate_grad_hook(sync.hook))
 
 
-def allreduce_head_grads(heads: Iterable[nn.Module], group=None, average: bool = True) -> int:
+def allreduce_head_grads(heads: Iterable[nn.Module], group=None, average: bool = True, bf16: bool = False) -> int:
     """Data-parallel training: all-reduce of the head gradients over flat fp32 buffers (NCCL over NVLink
     through the C ABI on GPUs, gloo in the CPU tests): one collective per flat gradient buffer of the fused
-    backward plus one for any other gradients of the head.  Returns the number of collectives issued."""
+    backward plus one for any other gradients of the head.  ``bf16``: the big flat buffers cross the link as bf16
+    (half the bytes; the loose remainder stays fp32).  Returns the number of collectives issued."""
     import torch.distributed as dist
 
     n = 0
@@ -163,19 +223,21 @@ def allreduce_head_grads(heads: Iterable[nn.Module], group=None, average: bool =
             groups.setdefault(g.untyped_storage().data_ptr(), []).append(g)
         # a collective that the backward already started on this head's flat buffer: only wait for it
         sync = getattr(getattr(head, "net", None), "_grad_sync", None)
+        if sync is not None:
+            sync.armed = None
         if sync is not None and sync.pending is not None:
             flat0, done = sync.pending
             sync.pending = None
+            done.wait(flat0.device)  # always: nothing below may touch the buffer while the collective rewrites it
             if groups.pop(flat0.untyped_storage().data_ptr(), None) is not None:
-                torch.cuda.current_stream(flat0.device).wait_event(done)
-                n += 1
+                n += 1  # .grad are views of the reduced buffer (checked when the collective was launched)
         loose = []
         for members in groups.values():
             flat = _shared_flat(members) if len(members) > 1 else None
             if flat is None:
                 loose.extend(members)
                 continue
-            _reduce_flat(flat, group, average, world)
+            _reduce_flat(flat, group, average, world, bf16)
             n += 1
         if loose:
             flat = torch.cat([g.reshape(-1) for g in loose])
