@@ -142,6 +142,31 @@ int uva_head_loss_bwd(UvaHead* h, const float* dloss, const float* target, const
                       float* dz, float* const* dparams /*host array of device ptrs*/,
                       void* ws, size_t ws_bytes, void* stream);
 
+/* MAR decoder tail fused into the head.  The reference computes the head's condition as
+ *   z = decoder_norm(x)[:, buffer_size_text:] + (diffusion_temporal_embed[t] + diffusion_spatial_embed[s])
+ * (mar_con_unified.py:702-724) and hands the fp32 z to DiffLoss.sample.  uva_head_sample_from_decoder takes the
+ * decoder output BEFORE decoder_norm instead: row r of the sampler is token tok = g % (T*S) of sample b = g / (T*S)
+ * with g = row_index[r] (or r when row_index == NULL; the gather z[mask_to_pred.nonzero()] of MAR:1090), read from
+ * x_dec[b, skip + tok, :]; LayerNorm + pos-embed run as the prologue of the cond_embed GEMM and write its bf16
+ * operand directly, so the fp32 z (403 MB per call at BASELINE config 3) never exists.  All other arguments as
+ * uva_head_sample.  uva_decoder_tail_rows writes the same rows as fp32 (for consumers that need z itself). */
+typedef struct {
+  const float* ln_w;       /* [Z] decoder_norm.weight */
+  const float* ln_b;       /* [Z] decoder_norm.bias */
+  const float* temporal;   /* [T, Z] diffusion_temporal_embed */
+  const float* spatial;    /* [S, Z] diffusion_spatial_embed */
+  float eps;               /* decoder_norm.eps (1e-6 for mar_base, MAR:1201) */
+  int32_t T, S;            /* frames, tokens per frame */
+  int64_t tokens_per_sample;  /* L: tokens per sample in x_dec (buffer_size_text + T*S with CLIP text tokens) */
+  int64_t skip;            /* leading tokens dropped (buffer_size_text, MAR:705-707) */
+} UvaDecoderTail;
+int uva_head_sample_from_decoder(UvaHead* h, const float* x_dec, const UvaDecoderTail* tail, const int64_t* row_index,
+                                 const float* x_init, const float* step_noise, const float* teacher, float* trace,
+                                 float temperature, float cfg_scale, int32_t clip_denoised, int32_t k_begin,
+                                 int32_t k_end, int64_t N, float* out, void* ws, size_t ws_bytes, void* stream);
+int uva_decoder_tail_rows(const float* x_dec, const UvaDecoderTail* tail, const int64_t* row_index, int64_t N,
+                          int32_t Z, float* z_out, void* stream);
+
 /* Fused AdamW + EMA update of a list of fp32 parameter tensors in ONE pass.  Replaces
  * torch.optim.AdamW.step() as configured by the reference (policy/unified_video_action_policy.py:325-360:
  * decoupled weight decay, 0 on 1-D tensors and biases) followed by EMAModel.step()

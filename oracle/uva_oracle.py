@@ -494,6 +494,19 @@ def diffactloss_forward(P, S: Schedule, target, z, t, noise, emulate_bf16: bool 
     return training_losses(P, S, target, t, noise, z, emulate_bf16)["loss"].mean()
 
 
+def decoder_tail(x_dec, ln_w, ln_b, eps, temporal, spatial, skip: int = 0):
+    """Tail of ``MAR.forward_mae_decoder`` (mar_con_unified.py:702-724): ``decoder_norm`` (nn.LayerNorm, eps 1e-6 for
+    mar_base, MAR:1201), drop the ``skip`` leading text tokens (MAR:705-707), add the diffusion position embedding
+    temporal[1,T,1,D] + spatial[1,1,S,D] reshaped to [1, T*S, D] (MAR:709-722).  x_dec [B, L, D] -> z [B, T*S, D]."""
+    D = x_dec.shape[-1]
+    x = F.layer_norm(x_dec, (D,), ln_w, ln_b, eps)
+    x = x[:, skip:]
+    T, S = temporal.shape[-2], spatial.shape[-2]
+    te = temporal.reshape(1, T, 1, D).expand(-1, -1, S, -1)
+    se = spatial.reshape(1, 1, S, D).expand(-1, T, -1, -1)
+    return x + (te + se).reshape(1, T * S, D)
+
+
 # --------------------------------------------------------------------------------------
 # Work counts (SURVEY.md §8(d)) — used by bench.py and DESIGN.md
 # --------------------------------------------------------------------------------------

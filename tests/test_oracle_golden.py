@@ -200,3 +200,14 @@ def test_other_channel_counts(golden_dir, A):
         dg = g[p + "tr_gdigest." + k]
         f = q.grad.double().flatten()
         np.testing.assert_allclose(np.array([f.abs().sum().item(), f.norm().item()]), dg[1:], rtol=1e-4, err_msg=k)
+
+
+def test_decoder_tail_restatement_vs_golden(golden_dir):
+    """oracle.decoder_tail (MAR:702-724) against the statements of the reference executed on nn.LayerNorm
+    (tests/golden/make_golden_tail.py): bit-exact, same ATen ops."""
+    g = np.load(os.path.join(golden_dir, "decoder_tail.npz"))
+    z = O.decoder_tail(torch.from_numpy(g["x_dec"]), torch.from_numpy(g["ln_w"]), torch.from_numpy(g["ln_b"]),
+                       float(g["eps"][0]), torch.from_numpy(g["temporal"]), torch.from_numpy(g["spatial"]),
+                       skip=int(g["meta"][4]))
+    assert z.shape == g["z"].shape
+    assert torch.equal(z, torch.from_numpy(g["z"]))

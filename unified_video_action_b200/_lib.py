@@ -65,6 +65,32 @@ class _Desc(ctypes.Structure):
     _fields_ = [(n, ctypes.c_int32) for n in ("C", "Z", "W", "depth", "T_train", "T_gen", "mode")]
 
 
+class _Tail(ctypes.Structure):
+    """UvaDecoderTail (include/uva_head.h)."""
+    _fields_ = [("ln_w", ctypes.c_void_p), ("ln_b", ctypes.c_void_p), ("temporal", ctypes.c_void_p),
+                ("spatial", ctypes.c_void_p), ("eps", ctypes.c_float), ("T", ctypes.c_int32), ("S", ctypes.c_int32),
+                ("tokens_per_sample", ctypes.c_int64), ("skip", ctypes.c_int64)]
+
+
+class DecoderTail:
+    """Host-side description of the MAR decoder tail (mar_con_unified.py:702-724) for ``Head.sample_from_decoder``:
+    ``decoder_norm`` weight / bias / eps, ``diffusion_temporal_embed`` [1,T,Z], ``diffusion_spatial_embed`` [1,S,Z],
+    the number of leading text tokens dropped.  Keeps the fp32 device tensors alive."""
+
+    def __init__(self, ln_weight, ln_bias, eps, temporal, spatial, skip: int = 0):
+        self.keep = [_f32c(t.detach(), "decoder tail") for t in (ln_weight, ln_bias, temporal, spatial)]
+        w, b, te, se = self.keep
+        Z = w.numel()
+        self.keep[2] = te = te.reshape(-1, Z)
+        self.keep[3] = se = se.reshape(-1, Z)
+        self.Z, self.T, self.S, self.skip, self.eps = Z, te.shape[0], se.shape[0], int(skip), float(eps)
+
+    def struct(self, tokens_per_sample: int) -> "_Tail":
+        w, b, te, se = self.keep
+        return _Tail(w.data_ptr(), b.data_ptr(), te.data_ptr(), se.data_ptr(), self.eps, self.T, self.S,
+                     int(tokens_per_sample), self.skip)
+
+
 _lib = None
 _lock = threading.Lock()
 
@@ -72,7 +98,7 @@ _lock = threading.Lock()
 SYMBOLS = [
     "uva_head_num_params", "uva_head_param_numel", "uva_head_create", "uva_head_destroy",
     "uva_schedule_table", "uva_head_load_weights", "uva_head_workspace_bytes", "uva_head_net_forward",
-    "uva_head_sample", "uva_head_loss_fwd", "uva_head_loss_bwd", "uva_head_launch_count",
+    "uva_head_sample", "uva_head_sample_from_decoder", "uva_decoder_tail_rows", "uva_head_loss_fwd", "uva_head_loss_bwd", "uva_head_launch_count",
     "uva_gemm_bf16_selftest", "uva_last_error", "uva_build_info", "uva_head_timing_enable", "uva_head_timing_read",
     "uva_adamw_ema_step", "uva_nccl_version", "uva_nccl_unique_id", "uva_nccl_comm_create", "uva_nccl_comm_destroy",
     "uva_head_allreduce_grads", "uva_head_allreduce_grads_bf16", "uva_head_set_noise_seed", "uva_philox_normal", "uva_head_set_train_reserve",
@@ -106,6 +132,11 @@ def lib() -> ctypes.CDLL:
         L.uva_head_net_forward.argtypes = [vp, vp, vp, vp, i64, vp, vp, ctypes.c_size_t, vp]
         L.uva_head_sample.restype = ctypes.c_int
         L.uva_head_sample.argtypes = [vp, vp, vp, vp, vp, vp, f32, f32, i32, i32, i32, i64, vp, vp, ctypes.c_size_t, vp]
+        L.uva_head_sample_from_decoder.restype = ctypes.c_int
+        L.uva_head_sample_from_decoder.argtypes = [vp, vp, ctypes.POINTER(_Tail), vp, vp, vp, vp, vp, f32, f32, i32, i32, i32,
+                                                   i64, vp, vp, ctypes.c_size_t, vp]
+        L.uva_decoder_tail_rows.restype = ctypes.c_int
+        L.uva_decoder_tail_rows.argtypes = [vp, ctypes.POINTER(_Tail), vp, i64, i32, vp, vp]
         L.uva_head_loss_fwd.restype = ctypes.c_int
         L.uva_head_loss_fwd.argtypes = [vp, vp, vp, vp, vp, vp, i64, vp, vp, vp, ctypes.c_size_t, vp]
         L.uva_head_loss_bwd.restype = ctypes.c_int
@@ -290,6 +321,40 @@ class Head:
                "uva_head_sample")
         return (out, tr) if trace else out
 
+    def sample_from_decoder(self, x_dec, tail: "DecoderTail", x_init, step_noise, temperature=1.0, cfg=1.0,
+                            clip_denoised=False, row_index=None, trace=False, k_begin=0, k_end=None, seed=None, offset=0):
+        """``sample`` with the condition rows taken from the MAR decoder output BEFORE ``decoder_norm``
+        (``x_dec`` [B, L, Z]): LayerNorm + diffusion pos-embed run inside the library as the prologue of the
+        cond_embed GEMM.  Rows: all B*T*S tokens, or ``row_index`` (int64 token-grid indices)."""
+        x_dec, x_init = _f32c(x_dec, "x_dec"), _f32c(x_init, "x_init")
+        if x_dec.dim() != 3 or x_dec.shape[2] != self.Z or tail.Z != self.Z:
+            raise RuntimeError("x_dec must be [B, L, Z] with the head's Z")
+        N = x_init.shape[0]
+        k_end = self.T_gen if k_end is None else k_end
+        if row_index is not None:
+            row_index = row_index.to(device=x_dec.device, dtype=torch.int64).contiguous()
+            if row_index.numel() != N:
+                raise RuntimeError("row_index must have one entry per sampled row")
+        if step_noise is None:
+            if seed is None:
+                raise RuntimeError("sample_from_decoder: pass step_noise or a seed for the in-kernel Philox generator")
+            _check(lib().uva_head_set_noise_seed(self._h, int(seed) & (2**64 - 1), int(offset) & 0xFFFFFFFF, 1),
+                   "uva_head_set_noise_seed")
+        else:
+            step_noise = _f32c(step_noise, "step_noise")
+        tr = torch.empty(k_end - k_begin, N, self.C, dtype=torch.float32, device=x_dec.device) if trace else None
+        out = torch.empty(N, self.C, dtype=torch.float32, device=x_dec.device)
+        if N == 0:
+            return (out, tr) if trace else out
+        ws = self.workspace(N, 0)
+        ts = tail.struct(x_dec.shape[1])
+        _check(lib().uva_head_sample_from_decoder(self._h, x_dec.data_ptr(), ctypes.byref(ts), _ptr(row_index),
+                                                  x_init.data_ptr(), _ptr(step_noise), None, _ptr(tr), float(temperature),
+                                                  float(cfg), int(bool(clip_denoised)), int(k_begin), int(k_end), N,
+                                                  out.data_ptr(), ws.data_ptr(), ws.numel(), _stream()),
+               "uva_head_sample_from_decoder")
+        return (out, tr) if trace else out
+
     def loss_fwd(self, target, z, mask, t, noise, want_rows=False):
         target, z, noise = _f32c(target, "target"), _f32c(z, "z"), _f32c(noise, "noise")
         mask = None if mask is None else _f32c(mask, "mask")
@@ -321,6 +386,22 @@ class Head:
                                        t.data_ptr(), noise.data_ptr(), N, dz.data_ptr(), arr, ws.data_ptr(),
                                        ws.numel(), _stream()), "uva_head_loss_bwd")
         return dz
+
+
+def decoder_tail_rows(x_dec: torch.Tensor, tail: DecoderTail, row_index: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """fp32 condition rows z [N, Z] = decoder_norm(x_dec)[:, skip:] + diffusion pos-embed (MAR:702-724) from the
+    library's decoder-tail kernel (what ``sample_from_decoder`` feeds to cond_embed, before the bf16 rounding)."""
+    x_dec = _f32c(x_dec, "x_dec")
+    B, L, Z = x_dec.shape
+    if row_index is not None:
+        row_index = row_index.to(device=x_dec.device, dtype=torch.int64).contiguous()
+    N = row_index.numel() if row_index is not None else B * tail.T * tail.S
+    out = torch.empty(N, Z, dtype=torch.float32, device=x_dec.device)
+    ts = tail.struct(L)
+    with torch.cuda.device(x_dec.device):
+        _check(lib().uva_decoder_tail_rows(x_dec.data_ptr(), ctypes.byref(ts), _ptr(row_index), N, Z, out.data_ptr(),
+                                           _stream()), "uva_decoder_tail_rows")
+    return out
 
 
 def philox_normal(seed: int, offset: int, step0: int, per_step: int, steps: int, device) -> torch.Tensor:

@@ -520,4 +520,84 @@ __global__ void k_ddpm_step(const float* __restrict__ net, int ldn, const float*
   }
 }
 
+// ------------------------------------------------------------------------------------------
+// Decoder tail -> condition rows (MAR.forward_mae_decoder, mar_con_unified.py:702-724):
+//   z[r, :] = LayerNorm_eps(x_dec[b, skip + tok, :]) * ln_w + ln_b + (temporal[tok / S, :] + spatial[tok % S, :])
+// with r = b * T*S + tok (row_index[r] replaces r when given: the gather z[mask_to_pred.nonzero()] of MAR:1090).
+// One warp per row, the row stays in registers (two-pass statistics like ATen's LayerNorm), and the result is
+// written ONCE as the operand type of cond_embed (bf16 in bf16 mode): the fp32 z of the reference never exists.
+// ------------------------------------------------------------------------------------------
+struct DecoderTail {
+  const float* x;          // [B, L, Z] decoder output BEFORE decoder_norm
+  const float* ln_w;       // [Z] decoder_norm.weight
+  const float* ln_b;       // [Z] decoder_norm.bias
+  const float* temporal;   // [T, Z] diffusion_temporal_embed
+  const float* spatial;    // [S, Z] diffusion_spatial_embed
+  const int64_t* row_index;  // optional [N]: token-grid index (b * T*S + tok) of output row r
+  float eps;
+  int T, S;
+  int64_t L, skip;         // tokens per sample in x, leading tokens dropped (buffer_size_text, MAR:705-707)
+};
+static const int DT_MAX_V4 = 8;  // Z <= 1024
+
+template <typename TO>
+__global__ void k_decoder_tail(DecoderTail p, int64_t row0, int64_t rows, int Z, TO* __restrict__ out) {
+  const int lane = threadIdx.x & 31;
+  const int nv = Z / 128;  // float4 per lane
+  const int64_t warps = (int64_t)gridDim.x * (blockDim.x >> 5);
+  for (int64_t r = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); r < rows; r += warps) {
+    const int64_t g = p.row_index ? p.row_index[row0 + r] : row0 + r;
+    const int64_t TS = (int64_t)p.T * p.S;
+    const int64_t b = g / TS;
+    const int tok = (int)(g - b * TS);
+    const float* xr = p.x + (b * p.L + p.skip + tok) * Z;
+    const float* te = p.temporal + (size_t)(tok / p.S) * Z;
+    const float* se = p.spatial + (size_t)(tok % p.S) * Z;
+    float4 v[DT_MAX_V4];
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < DT_MAX_V4; ++i)
+      if (i < nv) {
+        v[i] = *reinterpret_cast<const float4*>(xr + 128 * i + 4 * lane);
+        s += (v[i].x + v[i].y) + (v[i].z + v[i].w);
+      }
+#pragma unroll
+    for (int o = 16; o >= 1; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    const float mean = s / (float)Z;
+    float q = 0.f;
+#pragma unroll
+    for (int i = 0; i < DT_MAX_V4; ++i)
+      if (i < nv) {
+        const float a = v[i].x - mean, bq = v[i].y - mean, c = v[i].z - mean, d = v[i].w - mean;
+        q += (a * a + bq * bq) + (c * c + d * d);
+      }
+#pragma unroll
+    for (int o = 16; o >= 1; o >>= 1) q += __shfl_xor_sync(0xffffffffu, q, o);
+    const float rstd = rsqrtf(q / (float)Z + p.eps);
+#pragma unroll
+    for (int i = 0; i < DT_MAX_V4; ++i)
+      if (i < nv) {
+        const int j = 128 * i + 4 * lane;
+        const float4 w = __ldg(reinterpret_cast<const float4*>(p.ln_w + j));
+        const float4 bb = __ldg(reinterpret_cast<const float4*>(p.ln_b + j));
+        const float4 t4 = __ldg(reinterpret_cast<const float4*>(te + j));
+        const float4 s4 = __ldg(reinterpret_cast<const float4*>(se + j));
+        float o4[4];
+        o4[0] = ((v[i].x - mean) * rstd * w.x + bb.x) + (t4.x + s4.x);
+        o4[1] = ((v[i].y - mean) * rstd * w.y + bb.y) + (t4.y + s4.y);
+        o4[2] = ((v[i].z - mean) * rstd * w.z + bb.z) + (t4.z + s4.z);
+        o4[3] = ((v[i].w - mean) * rstd * w.w + bb.w) + (t4.w + s4.w);
+        TO* dst = out + r * Z + j;
+        if constexpr (sizeof(TO) == 2) {
+          TO o[4];
+#pragma unroll
+          for (int k = 0; k < 4; ++k) o[k] = from_f32<TO>(o4[k]);
+          *reinterpret_cast<uint2*>(dst) = *reinterpret_cast<uint2*>(o);
+        } else {
+          *reinterpret_cast<float4*>(dst) = make_float4(o4[0], o4[1], o4[2], o4[3]);
+        }
+      }
+  }
+}
+
 }  // namespace uva

@@ -190,6 +190,9 @@ struct UvaHead {
     StepCoef kc{};
   } fin;
   bool fuse_ddpm = true;
+  // set by uva_head_sample_from_decoder around the sampler: the condition rows come from the MAR decoder's
+  // pre-norm output through k_decoder_tail (LayerNorm + diffusion pos-embed) instead of a z tensor
+  struct TailSrc { bool on = false; DecoderTail t{}; } tail;
   bool pdl = true;       // UVA_PDL: programmatic dependent launch between the per-step kernels of the latency path
   bool pdl_big = true;   // UVA_PDL_BIG: programmatic dependent launch between the GEMMs of the chunked (throughput) path as well
   bool pdl_train = false;  // UVA_PDL_TRAIN (measured on the C2 step: 5.76 -> 5.82 ms, the side-stream head already fills the gaps; off)

@@ -330,6 +330,23 @@ class DiffLoss(nn.Module):
         return sample_rows(self.net, z, self.in_channels, self.num_sampling_steps, temperature, cfg, clip_denoised=False)
 
 
+    @torch.no_grad()
+    def sample_from_decoder(self, x_dec, decoder_norm, temporal_embed, spatial_embed, temperature=1.0, cfg=1.0,
+                            skip_tokens: int = 0, row_index=None):
+        """``sample(z)`` with ``z = decoder_norm(x_dec)[:, skip_tokens:] + diffusion pos-embed`` (the tail of
+        ``MAR.forward_mae_decoder``, mar_con_unified.py:702-724) computed inside the head: pass the decoder blocks'
+        output ``x_dec`` [B, L, Z], the ``decoder_norm`` LayerNorm module and the two embedding parameters
+        ([1,T,Z], [1,S,Z]).  Same RNG call order and the same samples as ``sample`` on the reference's z; the fp32 z
+        is never written.  ``row_index``: token-grid indices of the rows to sample
+        (``mask_to_pred.nonzero()`` flattened, MAR:1090); default all B*T*S tokens."""
+        _require_cuda(x_dec, "DiffLoss.sample_from_decoder")
+        tail = _lib.DecoderTail(decoder_norm.weight, decoder_norm.bias, decoder_norm.eps, temporal_embed, spatial_embed,
+                                skip=skip_tokens)
+        N = int(row_index.numel()) if row_index is not None else x_dec.shape[0] * tail.T * tail.S
+        return sample_rows(self.net, None, self.in_channels, self.num_sampling_steps, temperature, cfg, clip_denoised=False,
+                           decoder=(x_dec, tail, row_index, N))
+
+
 _NOISE_GRAPHS: dict = {}  # (device index, steps, N, C) -> (CUDAGraph, static [steps, N, C] buffer), latency regime only
 
 
@@ -364,12 +381,18 @@ def _step_noise(dev, steps: int, N: int, C: int) -> torch.Tensor:
 
 
 @torch.no_grad()
-def sample_rows(net: SimpleMLPAdaLN, z, C: int, steps: int, temperature: float, cfg: float, clip_denoised: bool):
+def sample_rows(net: SimpleMLPAdaLN, z, C: int, steps: int, temperature: float, cfg: float, clip_denoised: bool,
+                decoder=None):
     """The sampling tail shared by DiffLoss.sample (DL:68-90) and DiffActLoss.sample (DAL:207-227):
-    start noise from the CPU generator moved to the GPU, then the 100-step DDPM loop."""
-    _require_cuda(z, "sample")
-    dev = z.device
-    N = z.shape[0]
+    start noise from the CPU generator moved to the GPU, then the 100-step DDPM loop.  ``decoder`` =
+    (x_dec, DecoderTail, row_index, N): the condition rows come from the MAR decoder output instead of ``z``."""
+    if decoder is not None:
+        x_dec, tail, row_index, N = decoder
+        dev = x_dec.device
+    else:
+        _require_cuda(z, "sample")
+        dev = z.device
+        N = z.shape[0]
     if not cfg == 1.0:
         noise = torch.randn(N // 2, C).to(dev)
         noise = torch.cat([noise, noise], dim=0)
@@ -381,8 +404,14 @@ def sample_rows(net: SimpleMLPAdaLN, z, C: int, steps: int, temperature: float, 
         # [steps, N, C] tensor; the seed comes from torch's CPU generator so manual_seed still reproduces it
         seed = int(torch.randint(0, 2**62, (1,)).item())
         with torch.cuda.device(dev):
+            if decoder is not None:
+                return net.head().sample_from_decoder(x_dec, tail, noise, None, temperature=temperature, cfg=cfg,
+                                                      clip_denoised=clip_denoised, row_index=row_index, seed=seed)
             return net.head().sample(z, noise, None, temperature=temperature, cfg=cfg, clip_denoised=clip_denoised, seed=seed)
     # one CUDA randn per step, as th.randn_like(x) inside p_sample (GD:431)
     step_noise = _step_noise(dev, steps, N, C)
     with torch.cuda.device(dev):
+        if decoder is not None:
+            return net.head().sample_from_decoder(x_dec, tail, noise, step_noise, temperature=temperature, cfg=cfg,
+                                                  clip_denoised=clip_denoised, row_index=row_index)
         return net.head().sample(z, noise, step_noise, temperature=temperature, cfg=cfg, clip_denoised=clip_denoised)
