@@ -57,6 +57,13 @@ def _peaks():
     return 1590.0, 1400.0, "fallback"
 
 
+def _hbm_gbs():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"])
+    return 6650.0
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
 
@@ -201,11 +208,45 @@ def measure_latency(dev, batches=(1, 56), calls=200):
             ts.append((time.perf_counter() - t0) * 1e3)
         head.net.device_noise = None
         ts.sort()
-        out[f"B{B}_rows{16 * B}"]["p50_ms_device_noise"] = ts[len(ts) // 2]
+        e = out[f"B{B}_rows{16 * B}"]
+        e["p50_ms_device_noise"] = ts[len(ts) // 2]
+        # latency-regime roofline: every denoise step has to stream the bf16 weights once
+        wbytes = 2 * (2 * W + DEPTH * 5 * W * W + 2 * W * W + W * 4)  # input_proj, 6 x (AdaLN 3W^2 + MLP 2W^2), final AdaLN 2W^2, final linear
+        e["us_per_step"] = e["p50_ms"] * 1e3 / T_GEN
+        e["weight_gbs"] = wbytes * T_GEN / (e["p50_ms"] / 1e3) / 1e9
+        e["weight_floor_us_per_step"] = wbytes / (_hbm_gbs() * 1e9) * 1e6
     return out
 
 
-def measure_train(dev, world, B=16, iters=5, warmup=2):
+def measure_allreduce(dev, world, iters=10):
+    """The path's only collective, alone: the two heads' flat gradient buffers (35.75 M + 35.71 M fp32 values, what
+    the fused backward hands out) all-reduced through the C ABI, fp32 on the wire and bf16 on the wire.  Returns ms per
+    step (both heads) and the bus bandwidth 2 (N-1)/N * bytes / time (max over ranks is taken by the caller)."""
+    import torch
+
+    from unified_video_action_b200 import _lib
+
+    comm = _lib.GradComm()
+    flats = [torch.randn(n, device=dev) for n in (35749920, 35706884)]
+    out = {}
+    for name, bf16 in (("fp32", False), ("bf16", True)):
+        for f in flats:
+            comm.all_reduce_(f, True, bf16=bf16)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(iters):
+            for f in flats:
+                comm.all_reduce_(f, True, bf16=bf16)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / iters
+        wire = sum(f.numel() for f in flats) * (2 if bf16 else 4)
+        out[name] = {"ms": ms, "wire_bytes": wire, "bus_gbs": 2 * (world - 1) / world * wire / (ms / 1e3) / 1e9}
+    return out
+
+
+def measure_train(dev, world, B=16, iters=5, warmup=2, bf16_wire=False):
     """C2: one joint training step of the two heads (full_dynamic_model case): DiffLoss fwd+bwd on
     B x 1024 rows + DiffActLoss fwd+bwd on B x 16 rows, bf16 GEMMs, gradients wrt z and every head
     parameter; with world > 1 the head gradients are all-reduced over NCCL.  Returns rows/s
@@ -220,7 +261,7 @@ def measure_train(dev, world, B=16, iters=5, warmup=2):
     if world > 1 and os.environ.get("UVA_EARLY_ALLREDUCE", "1") != "0":
         from unified_video_action_b200 import overlap_allreduce
 
-        overlap_allreduce([vid, act])  # each head's all-reduce starts when its own backward ends
+        overlap_allreduce([vid, act], bf16=bf16_wire)  # each head's all-reduce starts when its own gradients are in place
     g = torch.Generator(device=dev).manual_seed(4321)
     z = torch.randn(B, 1024, Z, generator=g, device=dev, requires_grad=True)
     target = 0.2325 * torch.randn(B, 1024, C, generator=g, device=dev)
@@ -239,7 +280,7 @@ def measure_train(dev, world, B=16, iters=5, warmup=2):
             loss = vid(target, z, mask) + act(actions, z)
         loss.backward()
         if world > 1:
-            allreduce_head_grads([vid, act])
+            allreduce_head_grads([vid, act], bf16=bf16_wire)
         return loss
 
     # at least 30 untimed steps: the small head's fwd / bwd replay from CUDA graphs that the library captures the second
@@ -286,7 +327,104 @@ def measure_train(dev, world, B=16, iters=5, warmup=2):
     opt_ms = e0.elapsed_time(e1) / iters
     return {"ms_per_step": ms, "p50_ms": per[len(per) // 2], "max_ms": per[-1], "optimizer_ema_repack_ms": opt_ms, "rows_per_gpu": rows, "rows_per_s_per_gpu": rows / (ms / 1e3),
             "tflops_per_gpu": (B * 1024) * TRAIN_FLOP_PER_ROW / (ms / 1e3) / 1e12, "loss": float(loss.detach()),
+            "collective": ("none (1 GPU)" if world == 1 else
+                           f"NCCL all-reduce of the head gradients only (2 flat buffers, {'bf16' if bf16_wire else 'fp32'} on the wire), started from each head's backward"),
             "what": f"DiffLoss fwd+bwd {B}x1024 rows + DiffActLoss fwd+bwd {B}x16 rows (incl. its PyTorch pre-net), bf16"}
+
+
+def _max_over_ranks(x, dev, world):
+    import torch
+    import torch.distributed as dist
+
+    t = torch.tensor([float(x)], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def train_extras(dev, world):
+    """extras.C2_train at every N: the joint training step WITH the head-gradient all-reduce (the path's only
+    collective), fp32 and bf16 on the wire, plus the collective alone with its bus bandwidth.
+    Times are the max over ranks."""
+    res = measure_train(dev, world)
+    res["ms_per_step"] = _max_over_ranks(res["ms_per_step"], dev, world)
+    res["rows_per_s_per_gpu"] = res["rows_per_gpu"] / (res["ms_per_step"] / 1e3)
+    res["tflops_per_gpu"] = (res["rows_per_gpu"] - 16 * 16) * TRAIN_FLOP_PER_ROW / (res["ms_per_step"] / 1e3) / 1e12
+    if world > 1:
+        b = measure_train(dev, world, bf16_wire=True)
+        res["bf16_wire"] = {"ms_per_step": _max_over_ranks(b["ms_per_step"], dev, world), "p50_ms": b["p50_ms"]}
+        ar = measure_allreduce(dev, world)
+        for k in ar:
+            ar[k]["ms"] = _max_over_ranks(ar[k]["ms"], dev, world)
+            ar[k]["bus_gbs"] = 2 * (world - 1) / world * ar[k]["wire_bytes"] / (ar[k]["ms"] / 1e3) / 1e9
+        res["allreduce_alone"] = ar
+    return res
+
+
+def measure_gpu_eager(dev):
+    """Like-for-like GPU baseline: the reference head's op graph executed by stock
+    PyTorch eager kernels ON THE SAME B200 - the oracle port, which is the reference's torch code restated op for op
+    (the reference package itself cannot travel to the GPU box) - in fp32 with TF32 off (how the reference samples)
+    and under bf16 autocast.  C3-shaped: 8192 rows (cond || uncond, CFG 3.0) x 10 denoise steps; C1: 16 rows x 100
+    steps, clip_denoised.  Baseline measurement only: none of this is on the product path."""
+    import torch
+
+    from oracle import uva_oracle as O
+
+    P = {k: v.to(dev) for k, v in O.to_torch_params(O.make_params(C, Z, W, DEPTH, seed=1)).items()}
+    S = O.create_schedule(str(T_GEN))
+    out = {}
+    g = torch.Generator(device=dev).manual_seed(5)
+    for tag, rows, steps, cfg, clip in (("C3_8192rows_10steps", 8192, 10, CFG, False), ("C1_16rows_100steps", 16, 100, 1.0, True)):
+        z = torch.randn(rows, Z, generator=g, device=dev)
+        if cfg != 1.0:
+            h = torch.randn(rows // 2, C, generator=g, device=dev)
+            x0 = torch.cat([h, h])
+        else:
+            x0 = torch.randn(rows, C, generator=g, device=dev)
+        nz = torch.randn(steps, rows, C, generator=g, device=dev)
+        for name, ctx in (("fp32", torch.autocast("cuda", enabled=False)), ("bf16_autocast", torch.autocast("cuda", dtype=torch.bfloat16))):
+            with ctx:
+                O.sample_loop(P, S, z, x0, nz, temperature=TEMP, cfg=cfg, clip_denoised=clip, num_steps=min(steps, 3))
+                torch.cuda.synchronize()
+                t0 = time.perf_counter()
+                O.sample_loop(P, S, z, x0, nz, temperature=TEMP, cfg=cfg, clip_denoised=clip, num_steps=steps)
+                torch.cuda.synchronize()
+                dt = time.perf_counter() - t0
+            out[f"{tag}_{name}"] = {"row_steps_per_s": rows * steps / dt, "ms": dt * 1e3, "us_per_step": dt * 1e6 / steps}
+    out["what"] = "oracle port (the reference's torch op graph) run by PyTorch eager on this GPU; torch.backends.cuda.matmul.allow_tf32 = %s" % torch.backends.cuda.matmul.allow_tf32
+    return out
+
+
+def measure_libero(dev, B=32, calls=3):
+    """C4 (Libero10 / multi-view, MAR:1037-1041, 1101-1103, 1120-1122): one sample_tokens iteration =
+    diffactloss.sample (A = 10, clip_denoised, z [B,1024,768]) + diffloss.sample + diffloss_wrist.sample on the same
+    B x 1024 rows, cfg 1 (shipped configs), B = 32.  ms per iteration and row-steps/s over all three heads."""
+    import torch
+
+    vid, wrist, act = make_head(dev), make_head(dev), make_act_head(dev, A=10)
+    z = torch.randn(B, 1024, Z, device=dev)
+    rows = z.reshape(B * 1024, Z)
+
+    def it():
+        a = act.sample(z, TEMP, cfg=1.0)
+        v = vid.sample(rows, TEMP, 1.0)
+        w = wrist.sample(rows, TEMP, 1.0)
+        return a, v, w
+
+    it()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(calls):
+        a, v, w = it()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / calls
+    n = B * 16 + 2 * B * 1024
+    return {"ms_per_iteration": ms, "rows": n, "row_steps_per_s": n * T_GEN / (ms / 1e3), "B": B,
+            "step_tflops": (B * 16 * 2 * (10 * W + DEPTH * 5 * W * W + 2 * W * W + W * 20) + 2 * B * 1024 * FLOP_PER_ROW_STEP) * T_GEN / (ms / 1e3) / 1e12,
+            "what": "DiffActLoss.sample A=10 (B x 16 rows) + DiffLoss.sample + wrist DiffLoss.sample (B x 1024 rows each), 100 steps, cfg 1"}
 
 
 def measure_sweep(dev, sizes=(1024, 2048, 4096, 8192, 16384, 32768, 65536, 131072, 262144), dsteps=T_GEN):
@@ -358,7 +496,7 @@ def main():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="sample", choices=["sample", "train", "latency", "sweep"])
+    ap.add_argument("--workload", default="sample", choices=["sample", "train", "latency", "sweep", "libero", "eager"])
     ap.add_argument("--rows", type=int, default=131072, help="rows per GPU (cond || uncond)")
     ap.add_argument("--denoise-steps", type=int, default=T_GEN)
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
@@ -382,8 +520,26 @@ def main():
     os.environ["UVA_B200_PRECISION"] = args.precision
 
     if args.workload != "sample":
+        if args.workload in ("libero", "eager"):
+            line = None
+            if rank == 0:
+                if args.workload == "libero":
+                    line = {"metric": "diffusion-head token-steps/sec", "unit": "row-steps/s", "n_gpus": 1, "higher_is_better": True,
+                            "dtype": args.precision, "data": "synthetic", "config": {"workload": "C4: Libero10 multi-view sample_tokens iteration, B=32"},
+                            "detail": measure_libero(dev, calls=max(args.steps, 1))}
+                    line["value"] = line["detail"]["row_steps_per_s"]
+                else:
+                    line = {"metric": "diffusion-head token-steps/sec", "unit": "row-steps/s", "n_gpus": 1, "higher_is_better": True,
+                            "dtype": "f32 / bf16 autocast", "data": "synthetic", "impl": "pytorch-eager-on-gpu (baseline)",
+                            "config": {"workload": "reference op graph by PyTorch eager on this GPU"}, "detail": measure_gpu_eager(dev)}
+            if line is not None:
+                print(json.dumps(line), flush=True)
+            if world > 1:
+                dist.destroy_process_group()
+            return
         if args.workload == "train":
-            res = measure_train(dev, world, iters=max(args.steps, 1), warmup=max(args.warmup, 1))
+            res = measure_train(dev, world, iters=max(args.steps, 1), warmup=max(args.warmup, 1),
+                                bf16_wire=os.environ.get("UVA_BF16_WIRE", "0") != "0")
             t = torch.tensor([res["ms_per_step"]], device=dev, dtype=torch.float64)
             if world > 1:
                 dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -391,7 +547,7 @@ def main():
             line = {"metric": "diffusion-head training rows/sec (fwd+bwd)", "unit": "rows/s", "n_gpus": world,
                     "value": world * res["rows_per_gpu"] / (res["ms_per_step"] / 1e3), "ms_per_step": res["ms_per_step"],
                     "higher_is_better": True, "scaling": "weak", "dtype": args.precision, "data": "synthetic",
-                    "config": {"workload": "C2: " + res["what"], "collective": "flat fp32 all-reduce of head grads" if world > 1 else "none"},
+                    "config": {"workload": "C2: " + res["what"], "collective": res["collective"]},
                     "detail": res}
         elif args.workload == "latency":
             line = {"metric": "p50 predict_action head latency", "unit": "ms", "n_gpus": 1, "higher_is_better": False,
@@ -517,10 +673,20 @@ def main():
             rate, dt = cpu_sample_rate(crow, csteps)
             line["cpu_baseline"] = {"value": rate, "unit": "row-steps/s", "cores": torch.get_num_threads(), "kind": "port",
                                     "sample": f"{crow} rows x {csteps} denoise steps of the same CFG workload ({dt:.1f} s), fp32 torch CPU oracle port"}
-        if not args.no_extras and world == 1 and dsteps == T_GEN:
-            del z, x0, z_dev
-            torch.cuda.empty_cache()
-            line["extras"] = {"C1_latency": measure_latency(dev, calls=100), "C2_train": measure_train(dev, 1)}
+    extras_on = not args.no_extras and dsteps == T_GEN
+    if extras_on:
+        del z, x0, z_dev
+        torch.cuda.empty_cache()
+        # the training step with the path's only collective is measured at EVERY N (all ranks take part)
+        c2 = train_extras(dev, world)
+    if rank == 0:
+        if extras_on:
+            line["extras"] = {"C2_train": c2}
+            if world == 1:
+                line["extras"]["C1_latency"] = measure_latency(dev, calls=100)
+                line["extras"]["C4_libero"] = measure_libero(dev)
+                line["extras"]["C5_sweep"] = measure_sweep(dev, sizes=(1024, 2048, 4096, 8192, 16384, 32768, 65536))
+                line["extras"]["gpu_eager_baseline"] = measure_gpu_eager(dev)
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

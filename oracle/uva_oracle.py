@@ -142,11 +142,11 @@ def create_schedule(timestep_respacing="", diffusion_steps: int = 1000) -> Sched
 
 def _extract(arr: np.ndarray, t: torch.Tensor, shape, dtype) -> torch.Tensor:
     """``_extract_into_tensor`` (GD:892-904): float64 gather, cast, broadcast via + zeros."""
-    res = torch.from_numpy(arr)[t]
+    res = torch.from_numpy(arr).to(device=t.device)[t]  # like the reference: th.from_numpy(arr).to(device=timesteps.device)
     res = res.float() if dtype == torch.float32 else res.to(dtype)
     while res.dim() < len(shape):
         res = res[..., None]
-    return res + torch.zeros(shape, dtype=res.dtype)
+    return res + torch.zeros(shape, dtype=res.dtype, device=t.device)
 
 
 # --------------------------------------------------------------------------------------
@@ -253,7 +253,7 @@ def _linear(x, w, b, emulate_bf16=False, round_out=False):
 def timestep_embedding(t: torch.Tensor, dim: int = 256, max_period: int = 10000, dtype=torch.float32) -> torch.Tensor:
     """Sinusoidal embedding cos||sin (DL:110-134).  The reference computes it in fp32."""
     half = dim // 2
-    freqs = torch.exp(-math.log(max_period) * torch.arange(start=0, end=half, dtype=torch.float32) / half)
+    freqs = torch.exp(-math.log(max_period) * torch.arange(start=0, end=half, dtype=torch.float32) / half).to(device=t.device)
     if dtype == torch.float64:
         freqs = freqs.double()
         args = t[:, None].double() * freqs[None]
@@ -407,14 +407,14 @@ def sample_loop(
     T = S.num_timesteps
     n_run = T if num_steps is None else num_steps
     img = x_init
-    tmap = torch.from_numpy(S.timestep_map)
+    tmap = torch.from_numpy(S.timestep_map).to(device=x_init.device)
     states = []
     with torch.no_grad():
         for k in range(n_run):
             i = T - 1 - k
             if teacher is not None:
                 img = teacher[k]
-            t = torch.full((img.shape[0],), i, dtype=torch.long)
+            t = torch.full((img.shape[0],), i, dtype=torch.long, device=img.device)
             new_ts = tmap[t]  # _WrappedModel (RS:122-127)
             if cfg != 1.0:
                 out = net_forward_with_cfg(P, img, new_ts, z, cfg, emulate_bf16)
@@ -471,7 +471,7 @@ def training_losses(P, S: Schedule, x_start, t, noise, c, emulate_bf16: bool = F
     """GD:746-818 for LossType.MSE + LEARNED_RANGE + EPSILON.  Returns dict(loss, mse, vb) [N]."""
     C = x_start.shape[1]
     x_t = q_sample(S, x_start, t, noise)
-    new_ts = torch.from_numpy(S.timestep_map)[t]  # identity map for the training process (RS:122-127)
+    new_ts = torch.from_numpy(S.timestep_map).to(device=t.device)[t]  # identity map for the training process (RS:122-127)
     model_output = net_forward(P, x_t, new_ts, c, emulate_bf16)
     eps, var_values = torch.split(model_output, C, dim=1)
     frozen_out = torch.cat([eps.detach(), var_values], dim=1)
