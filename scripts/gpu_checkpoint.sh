@@ -4,6 +4,7 @@
 # steps (each writes gpurun_out/<tag>_<step>.*; a failing step does not stop the later ones):
 #   tests            python -m pytest tests -m gpu -x -q
 #   tests:<expr>     the same with -k <expr>
+#   testsall         the whole GPU suite without -x (every failure listed)
 #   smoke            __graft_entry__.smoke()
 #   bench            python bench.py --steps 3 --warmup 3            (default line with every extra)
 #   benchq           python bench.py --steps 3 --warmup 3 --no-extras --no-cpu-baseline
@@ -31,6 +32,7 @@ for step in "$@"; do
       if [ -n "$arg" ]; then timeout 1500 python -m pytest tests -m gpu -x -q -k "$arg" > ${O}_tests.log 2>&1
       else timeout 1500 python -m pytest tests -m gpu -x -q > ${O}_tests.log 2>&1; fi
       echo "rc=$?"; tail -n 15 ${O}_tests.log ;;
+    testsall) timeout 2400 python -m pytest tests -m gpu -q > ${O}_tests.log 2>&1; echo "rc=$?"; grep -E "^(FAILED|ERROR)|passed|failed" ${O}_tests.log | tail -n 30 ;;
     smoke) timeout 600 python __graft_entry__.py smoke > ${O}_smoke.log 2>&1; echo "rc=$?"; tail -n 4 ${O}_smoke.log ;;
     bench) timeout 900 python bench.py --steps 3 --warmup 3 > ${O}_bench.json 2> ${O}_bench.err; echo "rc=$?"; cut -c1-1500 ${O}_bench.json; tail -n 3 ${O}_bench.err ;;
     benchq) timeout 600 python bench.py --steps 3 --warmup 3 --no-extras --no-cpu-baseline > ${O}_benchq.json 2> ${O}_benchq.err; echo "rc=$?"; cut -c1-1200 ${O}_benchq.json; tail -n 3 ${O}_benchq.err ;;

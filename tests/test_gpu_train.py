@@ -6,7 +6,7 @@ Reference: DiffLoss.forward / DiffActLoss.forward (DL:44-66, DAL:145-166) -> tra
 with ragged row counts, masks with zeros, t = 0 rows (decoder NLL branch) and the action-head shape.
 
 Tolerances: fp32 mode <= 1e-4 relative (max-norm per tensor, against the tensor's own max); bf16 mode:
-loss <= 1e-2 relative, gradients <= 4e-2 relative L2 per tensor (bf16 operands in forward and backward
+loss <= 1e-2 relative, gradients <= 2e-2 relative L2 per tensor (bf16 operands in forward and backward
 GEMMs, fp32 accumulation; the reference trains under bf16 autocast the same way).
 """
 import os
@@ -21,7 +21,7 @@ pytestmark = pytest.mark.gpu
 
 FP32_TOL = 1e-4
 BF16_LOSS_TOL = 1e-2
-BF16_GRAD_L2 = 4e-2
+BF16_GRAD_L2 = 2e-2
 
 
 def _cuda():

@@ -478,11 +478,12 @@ def gemm_bf16_selftest(A: torch.Tensor, B: torch.Tensor, bias: Optional[torch.Te
     A.B; 2: A [K,M], B [K,N] -> A^T.B (split-K, reduced into a zero-filled D)."""
     assert A.dtype == torch.bfloat16 and B.dtype == torch.bfloat16 and A.is_cuda and B.is_cuda
     A, B = A.contiguous(), B.contiguous()
-    if layout & 7 == 2:
+    form = 0 if layout >= 24 else layout & 7  # 24, 25, 32, 33: forward form with a bf16 result (D holds bf16 [M, N])
+    if form == 2:
         K, M = A.shape
     else:
         M, K = A.shape
-    N = B.shape[0] if layout & 7 == 0 else B.shape[1]
+    N = B.shape[0] if form == 0 else B.shape[1]
     D = torch.zeros(M, N, dtype=torch.float32, device=A.device)
     _check(lib().uva_gemm_bf16_selftest(A.data_ptr(), B.data_ptr(), _ptr(bias), D.data_ptr(), M, N, K, block_n, layout, _stream()),
            "uva_gemm_bf16_selftest")
