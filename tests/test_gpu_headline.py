@@ -327,3 +327,36 @@ def test_pair_gemm_bf16_output_epilogues(layout, M, N, K):
     # bf16 output rounding (2^-9 relative) + the one-MUFU tanh.approx SiLU (<= 2^-10.5 absolute on tanh)
     err = (mine - ref).abs()
     assert float((err / (ref.abs() + 0.25)).max()) <= 8e-3, float((err / (ref.abs() + 0.25)).max())
+
+
+@pytest.mark.parametrize("N,cfg,group", [(300, 1.0, 0), (6000, 1.0, 1), (6000, 3.0, 0), (20000, 1.0, 16), (70000, 3.0, 0), (70000, 1.0, 5),
+                                         (3000, 1.0, 0), (5200, 2.0, 0)])
+def test_layer_chain_kernel_equals_per_layer_launches(P16, monkeypatch, N, cfg, group):
+    """The persistent layer-chain kernel (stack_kernel.cuh: all 19 tcgen05 GEMMs of a denoise step in one launch,
+    tiles ordered panel-major, layers chained through completion counters in global memory) runs the same MMAs in
+    the same order and the same epilogue arithmetic as the per-layer launches (UVA_STACK=0): bit-equal samples, for
+    every item order (0: the default diagonal wavefront; n > 0: groups of n tiles, 1 = the strictest dependency pattern) and across repeated calls
+    (a missed dependency shows up as a flaky mismatch)."""
+    dev = _cuda()
+    gen = torch.Generator().manual_seed(N + group)
+    steps = 2
+    z = torch.randn(N, 768, generator=gen).to(dev)
+    if cfg != 1.0:
+        half = torch.randn(N // 2, 16, generator=gen)
+        x0 = torch.cat([half, half]).to(dev)
+    else:
+        x0 = torch.randn(N, 16, generator=gen).to(dev)
+    nz = torch.randn(steps, N, 16, generator=gen).to(dev)
+    kw = dict(temperature=0.95, cfg=cfg, clip_denoised=False, k_begin=0, k_end=steps)
+    monkeypatch.setenv("UVA_SMALL_ROWS", "0")
+    monkeypatch.setenv("UVA_STACK", "0")
+    h_ref, _ = _head(16, P16, 1, dev)
+    ref = h_ref.sample(z, x0, nz, **kw)
+    l_ref = h_ref.launch_count()
+    monkeypatch.setenv("UVA_STACK", "1")
+    monkeypatch.setenv("UVA_STACK_GROUP", str(group))
+    h, _ = _head(16, P16, 1, dev)
+    for rep in range(4):
+        out = h.sample(z, x0, nz, **kw)
+        assert torch.equal(out, ref), (rep, float((out - ref).abs().max()))
+    assert h.launch_count() / 4 < 0.5 * l_ref  # 4 kernels per step and chunk instead of 22

@@ -166,6 +166,9 @@ __device__ __forceinline__ void bulk_wait_read_all() {}
 #else
 __device__ __forceinline__ void bulk_wait_read_all() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
 #endif
+// all but the N most recent bulk groups of this thread have finished reading their shared-memory source
+template <int N>
+__device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory"); }
 // all bulk groups of this thread are complete (writes visible)
 __device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 // named barrier among `threads` threads (whole warps) of the CTA

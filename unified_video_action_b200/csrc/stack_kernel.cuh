@@ -11,8 +11,10 @@
 // and the persistent clusters (one CTA pair per TPC, 256 x 256 tiles, cta_group::2 — the pipeline of
 // umma_gemm2.cuh) take items round-robin in that order.  A layer's tile may only start when the tiles it reads are
 // complete; completion is a counter per (layer, m-tile) in global memory:
-//   * every epilogue warp group signals  red.release.gpu  after its TMA stores have completed
-//     (cp.async.bulk.wait_group 0) and its row statistics are written  (4 signals per item: 2 CTAs x 2 groups);
+//   * the epilogue warps only compute and stage 32-column boxes in shared memory; ONE store thread per CTA (warp 2)
+//     issues the TMA stores, frees the staging slots when the stores have read them, waits for an item's stores to
+//     COMPLETE (cp.async.bulk.wait_group 0) and then signals  red.release.gpu  (2 signals per item: one per CTA) -
+//     no epilogue warp ever waits for a store;
 //   * the TMA producer polls  ld.acquire.gpu  on the counter of the layer that writes its A operand
 //     (u for GEMM2, a for GEMM1; the AdaLN GEMM reads ys, which exists before the launch, so 61 % of the MMA work
 //     never waits), issues  fence.proxy.async  and only then loads A — the weight box of the same pipeline stage is
@@ -38,7 +40,7 @@ struct StackLayer {
   int a_src;          // A operand: 0 = ys, 1 = a, 2 = u
   int w_row0;         // first row of this layer's weight in the [rows, W] weight map
   int dep_layer;      // layer whose completion (per m-tile) the A operand needs; -1: none
-  int dep_count;      // = 4 * n_tiles of that layer
+  int dep_count;      // = 2 * n_tiles of that layer (one signal per CTA of the pair and tile)
   int epi_dep_layer;  // layer whose completion the epilogue operands / overwritten buffers need; -1: none
   int epi_dep_count;
   int pad_;
@@ -53,8 +55,10 @@ struct StackArgs {
   StackLayer L[SK_MAX_LAYERS];
   int n_layers;
   int items_per_mtile;  // sum of n_tiles over the layers
-  int group;            // m-tiles per group
+  int group;            // > 0: m-tiles per group (group-major order); 0: diagonal wavefront order
   int W;
+  // diagonal order: P[l] = items of the layers < l of one m-tile, S[k] = sum_{i<k} P[i+1], Q[k] = sum_{i=1..k} P[i]
+  int P[SK_MAX_LAYERS + 1], S[SK_MAX_LAYERS + 1], Q[SK_MAX_LAYERS + 1];
   int64_t M;
   unsigned int* done;   // [n_layers][m_tiles], zero at launch
 };
@@ -71,7 +75,42 @@ struct SkItem {
   int64_t m;
 };
 
+// Item order.  group > 0: for group: for layer: for m-tile: for n-tile (a layer's tiles wait for the previous layer
+// of the same group: with 64 tiles per small layer and 74 clusters most of a layer boundary is a stall).
+// group == 0 (default): DIAGONAL WAVEFRONT.  Wave t holds, for every m-tile j with 0 <= t - j < n_layers, the tiles
+// of layer l = t - j: each m-tile advances one layer per wave and the m-tiles in flight are all at different layers,
+// so a tile and the tiles it depends on (same m-tile, previous layer) are a whole wave (all layers once = 128 tiles
+// for depth 6) apart in the item order, while only n_layers m-tiles (19 x 256 rows = 58 MB of activations, plus the
+// 71.5 MB of weights) are live at any time: they stay in L2.
+//   items before wave t:  C(t) = A(t) - B(t),  A(t) = t <= NL ? S[t] : S[NL] + (t - NL) ipm,  B(t) = t <= MT ? 0 : Q[t - MT]
+__device__ __forceinline__ int64_t sk_wave_start(const StackArgs& sa, int64_t t, int64_t MT) {
+  const int NL = sa.n_layers;
+  const int64_t a = t <= NL ? (int64_t)sa.S[t] : (int64_t)sa.S[NL] + (t - NL) * sa.items_per_mtile;
+  const int64_t b = t <= MT ? 0 : (int64_t)sa.Q[t - MT];
+  return a - b;
+}
+
 __device__ __forceinline__ SkItem sk_decode(const StackArgs& sa, int64_t item, int64_t m_tiles) {
+  SkItem it;
+  if (sa.group <= 0) {
+    const int NL = sa.n_layers;
+    int64_t lo = 0, hi = m_tiles + NL - 1;  // waves [lo, hi): largest t with C(t) <= item
+    while (hi - lo > 1) {
+      const int64_t mid = (lo + hi) >> 1;
+      if (sk_wave_start(sa, mid, m_tiles) <= item) lo = mid;
+      else hi = mid;
+    }
+    const int64_t t = lo;
+    const int l_lo = (int)(t - m_tiles + 1 > 0 ? t - m_tiles + 1 : 0);
+    const int l_hi = (int)(t < NL - 1 ? t : NL - 1);
+    const int r = (int)(item - sk_wave_start(sa, t, m_tiles)) + sa.P[l_lo];
+    int l = l_lo;
+    while (l < l_hi && r >= sa.P[l + 1]) ++l;
+    it.layer = l;
+    it.m = t - l;
+    it.n = r - sa.P[l];
+    return it;
+  }
   const int64_t per_group = (int64_t)sa.group * sa.items_per_mtile;
   const int64_t g = item / per_group;
   int64_t rem = item - g * per_group;
@@ -85,7 +124,6 @@ __device__ __forceinline__ SkItem sk_decode(const StackArgs& sa, int64_t item, i
     rem -= cnt;
   }
   const int nt = sa.L[l].n_tiles;
-  SkItem it;
   it.layer = l;
   it.m = m_first + rem / nt;
   it.n = (int)(rem % nt);
@@ -136,7 +174,9 @@ umma_stack_kernel(const __grid_constant__ StackMaps tm, const __grid_constant__ 
   uint64_t* tempty_bar = bars + 2 * kStages + 2;
   uint64_t* efull_bar = bars + 2 * kStages + 4;
   uint64_t* eempty_bar = bars + 2 * kStages + 4 + Cfg::kRing;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 4 + 2 * Cfg::kRing);
+  uint64_t* sready_bar = bars + 2 * kStages + 4 + 2 * Cfg::kRing;  // [kRing] box staged, ready for its TMA store
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 4 + 3 * Cfg::kRing);
+  static_assert((2 * kStages + 4 + 3 * Cfg::kRing) * 8 + 4 <= Cfg::kBarBytes, "barrier area");
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -165,10 +205,12 @@ umma_stack_kernel(const __grid_constant__ StackMaps tm, const __grid_constant__ 
     for (int s = 0; s < Cfg::kRing; ++s) {
       mbar_init(&efull_bar[s], 1);
       mbar_init(&eempty_bar[s], 1);
+      mbar_init(&sready_bar[s], 1);
     }
     fence_mbar_init();
   }
   if (warp == 2) tmem_alloc_2sm<Cfg::kTmemCols>(tmem_slot);
+  __syncwarp();
   tc_fence_before();
   cluster_sync_all();
   tc_fence_after();
@@ -234,6 +276,38 @@ umma_stack_kernel(const __grid_constant__ StackMaps tm, const __grid_constant__ 
       }
       if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
     }
+  } else if (warp == 2) {
+    // ===================== store thread: TMA stores of the staged boxes, slot release, completion signal =====================
+    if (elect_one()) {
+      uint32_t seq = 0;
+      for (int64_t item = cluster_id; item < num_items; item += num_clusters) {
+        const SkItem it = sk_decode(sa, item, m_tiles);
+        const StackLayer& L = sa.L[it.layer];
+        const int32_t r0cta = (int32_t)(it.m * BM2) + (int32_t)rank * UG_BM;
+        const bool ln_tile = L.kind == SK_LNMOD && it.n < L.ln_tiles;
+        const int nblk = ln_tile ? 4 : BN / 32;
+        const CUtensorMap* mo = ln_tile ? &tm.a_st : (L.kind == SK_GATED ? &tm.h : (L.kind == SK_SILU ? &tm.u_st : &tm.gate));
+        const int32_t c0 = ln_tile ? it.n * 128 : (L.kind == SK_LNMOD ? (it.n - L.ln_tiles) * BN : it.n * BN);
+        const uint32_t src_off = L.kind == SK_GATED ? 0u : (uint32_t)Cfg::kSlotH;
+        int prev_slot = -1;
+        for (int blk = 0; blk < nblk; ++blk, ++seq) {
+          const int slot = (int)(seq % Cfg::kRing);
+          const uint32_t ph = (seq / Cfg::kRing) & 1u;
+          mbar_wait(&sready_bar[slot], ph);
+          tma_store_2d(mo, epi_smem + slot * Cfg::kSlotBytes + src_off, c0 + 32 * blk, r0cta);
+          bulk_commit_group();
+          if (prev_slot >= 0) {
+            bulk_wait_read<1>();  // every store but the one just issued has read its box
+            mbar_arrive(&eempty_bar[prev_slot]);
+          }
+          prev_slot = slot;
+        }
+        bulk_wait_read<0>();
+        mbar_arrive(&eempty_bar[prev_slot]);
+        bulk_wait_all();  // this CTA's half of the item is in memory
+        sk_signal(sa.done + (int64_t)it.layer * m_tiles + it.m);
+      }
+    }
   } else if (warp == 3) {
     // ===================== epilogue operand prefetch / staging-slot relay =====================
     if (elect_one()) {
@@ -288,9 +362,7 @@ umma_stack_kernel(const __grid_constant__ StackMaps tm, const __grid_constant__ 
       const int rows_valid = left >= 32 ? 32 : (left > 0 ? (int)left : 0);
       const int64_t row = row0 + lane;
       const bool row_ok = lane < rows_valid;
-      const int32_t r0cta = (int32_t)(it.m * BM2) + (int32_t)rank * UG_BM;
       const uint32_t t_tile = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN);
-      unsigned int* done_me = sa.done + (int64_t)it.layer * m_tiles + it.m;
       if (L.kind == SK_LNMOD && n_blk < L.ln_tiles) {
         // (shift | scale) tile -> a = LN(h) (1 + scale) + shift for features f0 .. f0 + 127
         const int f0 = n_blk * 128;
@@ -354,13 +426,7 @@ umma_stack_kernel(const __grid_constant__ StackMaps tm, const __grid_constant__ 
             *reinterpret_cast<uint4*>(orow + ((i ^ rsw) << 4)) = make_uint4(pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
           fence_proxy_async();
           named_bar_sync(1 + cg, 128);
-          if (q == 0 && lane == 0) {
-            tma_store_2d(&tm.a_st, sp + Cfg::kSlotH, f0 + 32 * j, r0cta);
-            bulk_commit_group();
-            bulk_wait_read_all();
-            mbar_arrive(&eempty_bar[slot]);
-          }
-          __syncwarp();
+          if (q == 0 && lane == 0) mbar_arrive(&sready_bar[slot]);  // hand the box to the store thread
         }
         seq_base += 4;
       } else if (L.kind == SK_LNMOD || L.kind == SK_SILU) {
@@ -399,13 +465,7 @@ umma_stack_kernel(const __grid_constant__ StackMaps tm, const __grid_constant__ 
             *reinterpret_cast<uint4*>(orow + ((i ^ rsw) << 4)) = make_uint4(pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
           fence_proxy_async();
           named_bar_sync(1 + cg, 128);
-          if (q == 0 && lane == 0) {
-            tma_store_2d(mo, sp + Cfg::kSlotH, c_out + 32 * blk, r0cta);
-            bulk_commit_group();
-            bulk_wait_read_all();
-            mbar_arrive(&eempty_bar[slot]);
-          }
-          __syncwarp();
+          if (q == 0 && lane == 0) mbar_arrive(&sready_bar[slot]);  // hand the box to the store thread
         }
         seq_base += BN / 32;
       } else {
@@ -449,31 +509,21 @@ umma_stack_kernel(const __grid_constant__ StackMaps tm, const __grid_constant__ 
             ss += (o.x * o.x + o.y * o.y) + (o.z * o.z + o.w * o.w);
             *reinterpret_cast<float4*>(hrow + ((i ^ (r & 7)) << 4)) = o;
           }
+          // row sums of the new h: written before the last box is handed over, so that the store thread's
+          // completion signal (release) covers them
+          if (bi == BN / 64 - 1 && L.stats_out != nullptr && row_ok)
+            *reinterpret_cast<float2*>(L.stats_out + (row * (W / 128) + n_blk * 2 + cg) * 2) = make_float2(s, ss);
           fence_proxy_async();
           named_bar_sync(1 + cg, 128);
-          if (q == 0 && lane == 0) {
-            tma_store_2d(&tm.h, sp, n_blk * BN + blk * 32, r0cta);
-            bulk_commit_group();
-            bulk_wait_read_all();
-            mbar_arrive(&eempty_bar[slot]);
-          }
-          __syncwarp();
+          if (q == 0 && lane == 0) mbar_arrive(&sready_bar[slot]);  // hand the box to the store thread
         }
         seq_base += BN / 32;
-        if (L.stats_out != nullptr && row_ok)
-          *reinterpret_cast<float2*>(L.stats_out + (row * (W / 128) + n_blk * 2 + cg) * 2) = make_float2(s, ss);
       }
       // the accumulator stage is drained: hand it back before waiting for the stores
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive_cluster(&tempty_bar[acc], crank & ~1u);
       if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
-      // completion of this warp group's half of the item: stores landed, statistics written
-      named_bar_sync(1 + cg, 128);
-      if (q == 0 && lane == 0) {
-        bulk_wait_all();
-        sk_signal(done_me);
-      }
     }
   }
 

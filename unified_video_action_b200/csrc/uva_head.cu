@@ -21,6 +21,7 @@
 #include "train_kernels.cuh"
 #include "umma_gemm.cuh"
 #include "umma_gemm2.cuh"
+#include "stack_kernel.cuh"
 #include "chain_kernel.cuh"
 #include "final_ddpm.cuh"
 #include "optim.cuh"
@@ -190,6 +191,10 @@ struct UvaHead {
     StepCoef kc{};
   } fin;
   bool fuse_ddpm = true;
+  // UVA_STACK: all tcgen05 GEMMs of a denoise step in ONE persistent launch, panel-major so that a row panel's
+  // activations stay in L2 between the layers (stack_kernel.cuh).  UVA_STACK_GROUP: 256-row tiles per panel group.
+  bool stack = true;
+  int stack_group = 0;  // 0: diagonal wavefront order (default); > 0: group-major order with that many 256-row tiles per group
   // set by uva_head_sample_from_decoder around the sampler: the condition rows come from the MAR decoder's
   // pre-norm output through k_decoder_tail (LayerNorm + diffusion pos-embed) instead of a z tensor
   struct TailSrc { bool on = false; DecoderTail t{}; } tail;
@@ -240,7 +245,7 @@ struct UvaHead {
   struct TimedLaunch { int cat; cudaEvent_t a, b; };
   std::vector<TimedLaunch> timed;
 };
-enum { CAT_ADA = 0, CAT_MLP1, CAT_MLP2, CAT_FINAL, CAT_COND, CAT_OTHER, CAT_COUNT };
+enum { CAT_ADA = 0, CAT_MLP1, CAT_MLP2, CAT_FINAL, CAT_COND, CAT_OTHER, CAT_STACK, CAT_COUNT };
 
 #define LAUNCH_CHECK(h)                                                                       \
   do {                                                                                        \
@@ -363,6 +368,8 @@ extern "C" int uva_head_create(const UvaHeadDesc* desc, UvaHead** out) {
   if (const char* e = getenv("UVA_PAIR")) h->pair = atoi(e) != 0;
   if (const char* e = getenv("UVA_QUAD")) h->quad = atoi(e) != 0;
   if (const char* e = getenv("UVA_FUSE_LN")) h->fuse_ln = atoi(e) != 0;
+  if (const char* e = getenv("UVA_STACK")) h->stack = atoi(e) != 0;
+  if (const char* e = getenv("UVA_STACK_GROUP")) { int v = atoi(e); if (v >= 0 && v <= 4096) h->stack_group = v; }
 #ifdef UVA_DEBUG  // result-corrupting timing switches exist only in a -DUVA_DEBUG build, never in the shipped library
   if (const char* e = getenv("UVA_DEBUG_SKIP")) h->dbg_skip = atoi(e);
 #endif
