@@ -354,6 +354,7 @@ def test_layer_chain_kernel_equals_per_layer_launches(P16, monkeypatch, N, cfg, 
     ref = h_ref.sample(z, x0, nz, **kw)
     l_ref = h_ref.launch_count()
     monkeypatch.setenv("UVA_STACK", "1")
+    monkeypatch.setenv("UVA_STACK_ROWS", "1000000")  # also where the default policy prefers the per-layer launches
     monkeypatch.setenv("UVA_STACK_GROUP", str(group))
     h, _ = _head(16, P16, 1, dev)
     for rep in range(4):

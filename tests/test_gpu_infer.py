@@ -268,6 +268,7 @@ def test_latency_path_equals_chunked_path(video, monkeypatch, N, cfg, clip, k_en
     nz = torch.randn(k_end, N, 16, generator=gen)
     args = (z.to(dev), x0.to(dev), nz.to(dev))
     kw = dict(temperature=0.95, cfg=cfg, clip_denoised=clip, k_begin=0, k_end=k_end)
+    monkeypatch.setenv("UVA_SMALL_ROWS", "2048")  # the latency path's own limit (the default hands over at 1024 rows)
     h = _head(16, 768, 1024, 6, P, 1, dev)
     l0 = h.launch_count()
     outs = [h.sample(*args, **kw).cpu() for _ in range(3)]

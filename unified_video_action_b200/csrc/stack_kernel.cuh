@@ -432,8 +432,6 @@ umma_stack_kernel(const __grid_constant__ StackMaps tm, const __grid_constant__ 
       } else if (L.kind == SK_LNMOD || L.kind == SK_SILU) {
         // bf16 output tile: gate = acc + bias (AdaLN gate third) or u = SiLU(acc + bias) (GEMM1)
         const bool silu = L.kind == SK_SILU;
-        const CUtensorMap* mo = silu ? &tm.u_st : &tm.gate;
-        const int c_out = silu ? n_blk * BN : (n_blk - L.ln_tiles) * BN;
         mbar_wait(&tfull_bar[acc], acc_phase);
         tc_fence_after();
 #pragma unroll 1

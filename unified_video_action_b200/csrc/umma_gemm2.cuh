@@ -11,7 +11,7 @@
 //
 //   warp 0 : TMA producer (both CTAs; completion bytes of both land on the LEADER's full barrier)
 //   warp 1 : MMA issuer (leader CTA only); tcgen05.commit multicasts to the barriers of both CTAs
-//   warp 2 : tensor-memory allocator (cta_group::2 allocation, both CTAs)
+//   warp 2 : tensor-memory allocator (cta_group::2 allocation, both CTAs); afterwards the store thread of the TMA-fed epilogues
 //   warps 4-11: epilogue of this CTA's 128 rows; accumulator stage release = remote arrive on the
 //           leader's barrier (16 arrivals: 8 warps x 2 CTAs)
 #pragma once
@@ -79,7 +79,9 @@ umma_gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   uint64_t* tempty_bar = bars + 2 * kStages + 2;  // [2]       (used in the leader CTA)
   uint64_t* efull_bar = bars + 2 * kStages + 4;                  // [kRing] epilogue prefetch ring (this CTA)
   uint64_t* eempty_bar = bars + 2 * kStages + 4 + Cfg::kRing;    // [kRing]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 4 + 2 * Cfg::kRing);
+  uint64_t* sready_bar = bars + 2 * kStages + 4 + 2 * Cfg::kRing;  // [kRing] box staged by the epilogue warps, ready for its TMA store
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 4 + 3 * Cfg::kRing);
+  static_assert((2 * kStages + 4 + 3 * Cfg::kRing) * 8 + 4 <= Cfg::kBarBytes, "barrier area");
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -121,10 +123,12 @@ umma_gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     for (int s = 0; s < Cfg::kRing; ++s) {
       mbar_init(&efull_bar[s], 1);
       mbar_init(&eempty_bar[s], 1);
+      mbar_init(&sready_bar[s], 1);
     }
     fence_mbar_init();
   }
   if (warp == 2) tmem_alloc_2sm<Cfg::kTmemCols>(tmem_slot);
+  __syncwarp();
   tc_fence_before();
   cluster_sync_all();
   tc_fence_after();
@@ -207,6 +211,56 @@ umma_gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       }
       if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
     }
+  } else if (warp == 2) {
+    // ===================== store thread (TMA-fed epilogue kinds) =====================
+    // The epilogue warps only stage 32-column boxes in the ring; this thread issues their TMA stores and frees a
+    // slot when its store has read it, so no epilogue warp ever waits for a store (they used to: ~0.3 us per box).
+    if constexpr (Cfg::kTmaEpi) {
+      if (elect_one()) {
+        uint32_t seq = 0;
+        int prev_slot = -1;
+        for (int64_t item = cluster_id; item < num_items; item += num_clusters) {
+          int64_t m_blk; int n_blk;
+          ug_tile_coords(item / splits, m_tiles, n_tiles, gm, m_blk, n_blk);
+          n_blk = n_blk * kPairs + (int)pair;
+          const int32_t r0cta = (int32_t)(m_blk * BM2) + (int32_t)rank * UG_BM;
+          const bool ln_tile = (KIND == EPI_LNMOD) && n_blk < ep.ln_tiles;
+          const int nblk = ln_tile ? 4 : BN / 32;
+          for (int blk = 0; blk < nblk; ++blk, ++seq) {
+            const int slot = (int)(seq % Cfg::kRing);
+            const uint32_t ph = (seq / Cfg::kRing) & 1u;
+            mbar_wait(&sready_bar[slot], ph);
+            uint8_t* sp = epi_smem + slot * Cfg::kSlotBytes;
+            const int32_t cc = n_blk * BN + 32 * blk;
+            if constexpr (KIND == EPI_LNMOD) {
+              if (ln_tile) tma_store_2d(&em.g, sp + Cfg::kSlotH, n_blk * 128 + 32 * blk, r0cta);
+              else tma_store_2d(&em.h_out, sp + Cfg::kSlotH, (n_blk - ep.ln_tiles) * BN + 32 * blk, r0cta);
+            } else if constexpr (KIND == EPI_GATED_RES) {
+              tma_store_2d(&em.h_out, sp, cc, r0cta);
+            } else if constexpr (KIND == EPI_SILU_SAVE) {
+              tma_store_2d(&em.h_out, sp + Cfg::kSlotH, cc, r0cta);
+              tma_store_2d(&em.g, sp, cc, r0cta);
+            } else if constexpr (KIND == EPI_GATED_SAVE) {
+              tma_store_2d(&em.h_out, sp, cc, r0cta);
+              tma_store_2d(&em.b2, sp + Cfg::kSlotH, cc, r0cta);
+            } else {  // SILU_ACT, STORE_ACT, DSILU_ACT: one bf16 box
+              tma_store_2d(&em.h_out, sp + Cfg::kSlotH, cc, r0cta);
+            }
+            bulk_commit_group();
+            if (prev_slot >= 0) {
+              bulk_wait_read<1>();  // every store but the one just issued has read its box
+              mbar_arrive(&eempty_bar[prev_slot]);
+            }
+            prev_slot = slot;
+          }
+        }
+        if (prev_slot >= 0) {
+          bulk_wait_read<0>();
+          mbar_arrive(&eempty_bar[prev_slot]);
+        }
+        bulk_wait_all();  // this thread's TMA stores have landed
+      }
+    }
   } else if (warp == 3) {
     // ===================== epilogue operand prefetch (TMA-fed epilogue kinds) =====================
     if constexpr (Cfg::kTmaEpi) {
@@ -272,7 +326,6 @@ umma_gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       if constexpr (KIND == EPI_LNMOD) {
         const int W = ep.ln_width;
         const int r = q * 32 + lane;  // row inside this CTA's 128-row box
-        const int32_t r0cta = (int32_t)(m_blk * BM2) + (int32_t)rank * UG_BM;
         const uint32_t rsw = (uint32_t)((r >> 1) & 3);
         if (n_blk < ep.ln_tiles) {
           // (shift | scale) tile: warp group cg takes the 32-feature boxes j = cg, cg + 2 of features f0 .. f0+127
@@ -333,18 +386,11 @@ umma_gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
               *reinterpret_cast<uint4*>(orow + ((i ^ rsw) << 4)) = make_uint4(pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
             fence_proxy_async();
             named_bar_sync(1 + cg, 128);
-            if (q == 0 && lane == 0) {
-              tma_store_2d(&em.g, sp + Cfg::kSlotH, f0 + 32 * j, r0cta);
-              bulk_commit_group();
-              bulk_wait_read_all();
-              mbar_arrive(&eempty_bar[slot]);
-            }
-            __syncwarp();
+            if (q == 0 && lane == 0) mbar_arrive(&sready_bar[slot]);  // hand the box to the store thread (warp 2)
           }
           seq_base += 4;
         } else {
           // gate tile: bf16 boxes into out2 (h_out map)
-          const int g0 = (n_blk - ep.ln_tiles) * BN;
           mbar_wait(&tfull_bar[acc], acc_phase);
           tc_fence_after();
 #pragma unroll 1
@@ -369,13 +415,7 @@ umma_gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
               *reinterpret_cast<uint4*>(orow + ((i ^ rsw) << 4)) = make_uint4(pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
             fence_proxy_async();
             named_bar_sync(1 + cg, 128);
-            if (q == 0 && lane == 0) {
-              tma_store_2d(&em.h_out, sp + Cfg::kSlotH, g0 + 32 * blk, r0cta);
-              bulk_commit_group();
-              bulk_wait_read_all();
-              mbar_arrive(&eempty_bar[slot]);
-            }
-            __syncwarp();
+            if (q == 0 && lane == 0) mbar_arrive(&sready_bar[slot]);  // hand the box to the store thread (warp 2)
           }
           seq_base += BN / 32;
         }
@@ -383,7 +423,6 @@ umma_gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         // h[rows, cols] = h + gate * (acc + bias) on the fp32 residual stream + row sums for the next LayerNorm.
         // Warp group cg takes the 32-column boxes blk = cg, cg + 2, ... of the prefetch ring.
         const int r = q * 32 + lane;  // row inside this CTA's 128-row box
-        const int32_t r0cta = (int32_t)(m_blk * BM2) + (int32_t)rank * UG_BM;
         float s = 0.f, ss = 0.f;
         mbar_wait(&tfull_bar[acc], acc_phase);
         tc_fence_after();
@@ -425,20 +464,13 @@ umma_gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           }
           fence_proxy_async();
           named_bar_sync(1 + cg, 128);
-          if (q == 0 && lane == 0) {
-            tma_store_2d(&em.h_out, sp, n_blk * BN + blk * 32, r0cta);
-            bulk_commit_group();
-            bulk_wait_read_all();
-            mbar_arrive(&eempty_bar[slot]);
-          }
-          __syncwarp();
+          if (q == 0 && lane == 0) mbar_arrive(&sready_bar[slot]);  // hand the box to the store thread (warp 2)
         }
         if (ep.stats != nullptr && row_ok)
           *reinterpret_cast<float2*>(ep.stats + (row * (ep.ln_width / 128) + n_blk * 2 + cg) * 2) = make_float2(s, ss);
       } else if constexpr (KIND == EPI_SILU_ACT || KIND == EPI_STORE_ACT) {
         // out(bf16) = f(acc + bias): 32-column boxes staged in the ring and written with TMA stores (h_out map)
         const int r = q * 32 + lane;
-        const int32_t r0cta = (int32_t)(m_blk * BM2) + (int32_t)rank * UG_BM;
         const uint32_t rsw = (uint32_t)((r >> 1) & 3);
         mbar_wait(&tfull_bar[acc], acc_phase);
         tc_fence_after();
@@ -471,13 +503,7 @@ umma_gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             *reinterpret_cast<uint4*>(orow + ((i ^ rsw) << 4)) = make_uint4(pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
           fence_proxy_async();
           named_bar_sync(1 + cg, 128);
-          if (q == 0 && lane == 0) {
-            tma_store_2d(&em.h_out, sp + Cfg::kSlotH, n_blk * BN + 32 * blk, r0cta);
-            bulk_commit_group();
-            bulk_wait_read_all();
-            mbar_arrive(&eempty_bar[slot]);
-          }
-          __syncwarp();
+          if (q == 0 && lane == 0) mbar_arrive(&sready_bar[slot]);  // hand the box to the store thread (warp 2)
         }
       } else if constexpr (KIND == EPI_DSILU_ACT || KIND == EPI_SILU_SAVE || KIND == EPI_GATED_SAVE) {
         // training kinds on the same ring (32-column boxes, warp group cg takes blk = cg, cg + 2, ...):
@@ -485,7 +511,6 @@ umma_gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         //   SILU_SAVE : out2 = p = acc + bias, out = SiLU(p)      two bf16 output boxes (g part: out, h part: out2)
         //   GATED_SAVE: q = acc + bias -> out2(bf16); out(f32) = res + gate * q   (res / gate prefetched)
         const int r = q * 32 + lane;
-        const int32_t r0cta = (int32_t)(m_blk * BM2) + (int32_t)rank * UG_BM;
         const uint32_t rsw = (uint32_t)((r >> 1) & 3);
         mbar_wait(&tfull_bar[acc], acc_phase);
         tc_fence_after();
@@ -583,22 +608,7 @@ umma_gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             *reinterpret_cast<uint4*>(grow + ((i ^ rsw) << 4)) = make_uint4(pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
           fence_proxy_async();
           named_bar_sync(1 + cg, 128);
-          if (q == 0 && lane == 0) {
-            const int32_t cc = n_blk * BN + 32 * blk;
-            if constexpr (KIND == EPI_DSILU_ACT) {
-              tma_store_2d(&em.h_out, sp + Cfg::kSlotH, cc, r0cta);
-            } else if constexpr (KIND == EPI_SILU_SAVE) {
-              tma_store_2d(&em.h_out, sp + Cfg::kSlotH, cc, r0cta);
-              tma_store_2d(&em.g, sp, cc, r0cta);
-            } else {
-              tma_store_2d(&em.h_out, sp, cc, r0cta);
-              tma_store_2d(&em.b2, sp + Cfg::kSlotH, cc, r0cta);
-            }
-            bulk_commit_group();
-            bulk_wait_read_all();
-            mbar_arrive(&eempty_bar[slot]);
-          }
-          __syncwarp();
+          if (q == 0 && lane == 0) mbar_arrive(&sready_bar[slot]);  // hand the box to the store thread (warp 2)
         }
       } else {
         typename RowEpi<KIND, TA>::Pre pre;
@@ -624,9 +634,6 @@ umma_gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     }
   }
 
-  if constexpr (Cfg::kTmaEpi) {
-    if (warp >= 4 && (warp & 3) == 0 && lane == 0) bulk_wait_all();  // this thread's TMA stores have landed
-  }
   tc_fence_before();
   cluster_sync_all();
   if (warp == 2) {

@@ -176,6 +176,11 @@ struct UvaHead {
   cudaStream_t side = nullptr;
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   bool overlap = true;
+  // UVA_LANE_SPLIT: while two chunk lanes are in flight each lane's persistent GEMM grids take HALF of the SMs, so that
+  // two GEMMs of different kinds really run side by side (the HBM-bound gated-residual GEMM of one lane next to a
+  // tensor-bound one of the other) instead of alternating whole-chip kernels
+  // (measured, C3 at 131072 rows: 14.14 / 14.49 -> 14.63 / 14.69 M row-steps/s under the same power cap)
+  bool lane_split = true;
   bool pair = true;  // CTA-pair (cta_group::2) GEMM for M > 128
   bool quad = false;  // UVA_QUAD: clusters of two CTA pairs with multicast A boxes (forward-form GEMMs)
   bool fuse_ln = true;  // UVA_FUSE_LN: LayerNorm-modulate inside the AdaLN GEMM epilogue (bf16 sampling path)
@@ -193,8 +198,13 @@ struct UvaHead {
   bool fuse_ddpm = true;
   // UVA_STACK: all tcgen05 GEMMs of a denoise step in ONE persistent launch, panel-major so that a row panel's
   // activations stay in L2 between the layers (stack_kernel.cuh).  UVA_STACK_GROUP: 256-row tiles per panel group.
+  // Measured (profiles/r02_stack_*): one launch per step wins where the per-layer launches are short - 4096 rows 39.2 ->
+  // 33.4 ms per 100-step call, 8192 rows 68.5 -> 61.0, 16384 rows 128.1 -> 118.0, even at 32768 - and loses from 65536
+  // rows on (the rows in flight that hide the layer-to-layer dependency latency no longer fit L2), so it takes calls
+  // of up to stack_rows rows (UVA_STACK_ROWS), as ONE chunk.
   bool stack = true;
-  int stack_group = 0;  // 0: diagonal wavefront order (default); > 0: group-major order with that many 256-row tiles per group
+  int64_t stack_rows = 32768;
+  int stack_group = 32;  // 256-row tiles per group of the group-major item order; 0: diagonal wavefront order
   // set by uva_head_sample_from_decoder around the sampler: the condition rows come from the MAR decoder's
   // pre-norm output through k_decoder_tail (LayerNorm + diffusion pos-embed) instead of a z tensor
   struct TailSrc { bool on = false; DecoderTail t{}; } tail;
@@ -220,7 +230,7 @@ struct UvaHead {
   // UVA_SMALL_ROWS: largest batch that takes the latency path.  Measured (100-step call, cfg 1): 1536 rows 35.8 -> 27.4 ms
   // and 2048 rows 37.1 -> 29.6 ms against the chunked path (whose 256 x 256 pair tiles fill only 48 - 64 SMs there);
   // even at 3072 rows, 4 % slower at 4096.  The modulation table of all steps costs 4.1 MB per row (8.4 GB at 2048).
-  int64_t small_rows = 2048;
+  int64_t small_rows = 1024;  // (2048 before the layer-chain kernel existed: 1536 rows 28.6 -> 25.9 ms, 2048 rows 32.9 -> 26.4 ms on it)
   StepCoef* d_coef = nullptr;    // [T_gen] DDPM update coefficients of the sampling process, by timestep index
   bool use_chain = true;         // UVA_CHAIN: persistent chain kernel (chain_kernel.cuh)
   int64_t chain_rows = 32;       // UVA_CHAIN_ROWS: largest batch it takes (its time grows with rows / 16)
@@ -365,10 +375,12 @@ extern "C" int uva_head_create(const UvaHeadDesc* desc, UvaHead** out) {
     if (v >= 256) h->chunk_rows = (v / 256) * 256;
   }
   if (const char* e = getenv("UVA_OVERLAP")) h->overlap = atoi(e) != 0;
+  if (const char* e = getenv("UVA_LANE_SPLIT")) h->lane_split = atoi(e) != 0;
   if (const char* e = getenv("UVA_PAIR")) h->pair = atoi(e) != 0;
   if (const char* e = getenv("UVA_QUAD")) h->quad = atoi(e) != 0;
   if (const char* e = getenv("UVA_FUSE_LN")) h->fuse_ln = atoi(e) != 0;
   if (const char* e = getenv("UVA_STACK")) h->stack = atoi(e) != 0;
+  if (const char* e = getenv("UVA_STACK_ROWS")) { long v = atol(e); if (v >= 0) h->stack_rows = v; }
   if (const char* e = getenv("UVA_STACK_GROUP")) { int v = atoi(e); if (v >= 0 && v <= 4096) h->stack_group = v; }
 #ifdef UVA_DEBUG  // result-corrupting timing switches exist only in a -DUVA_DEBUG build, never in the shipped library
   if (const char* e = getenv("UVA_DEBUG_SKIP")) h->dbg_skip = atoi(e);
