@@ -167,6 +167,27 @@ int uva_head_sample_from_decoder(UvaHead* h, const float* x_dec, const UvaDecode
 int uva_decoder_tail_rows(const float* x_dec, const UvaDecoderTail* tail, const int64_t* row_index, int64_t N,
                           int32_t Z, float* z_out, void* stream);
 
+/* DiffActLoss pre-net fused into the library.  The reference runs, in front of the action /
+ * proprioception head (diffusion_action_loss.py:41-61, 112-124 == 169-181, act_model_type "conv_fc"):
+ *   z [B, n_frames * 256, Z] -> n_frames 16 x 16 token maps -> Conv2d(Z, Z, 3, padding 1) + ReLU + AdaptiveAvgPool2d(4, 4)
+ *   -> Linear(16 Z, Z) + ReLU + Linear(Z, Z) -> Linear(n_frames -> 16) over time -> Linear + ReLU + Linear -> [B, 16, Z]
+ * as ~25 cuDNN / cuBLAS / elementwise launches.  Here the convolution is ONE implicit-GEMM launch of the CTA-pair tcgen05
+ * kernel (operands gathered by 4D TMA boxes from the token tensor, padding = TMA zero fill, bias + ReLU + average pool in
+ * the epilogue) and the Linears are tcgen05 GEMMs; the backward uses the same cores (data gradient = the gather with
+ * flipped taps, weight gradient = gathered B operand).  bf16 operands, fp32 accumulation; handles created in bf16 mode only.
+ *   params / dparams: 12 device pointers in the reference's state_dict order - conv.0.{weight [Z,Z,3,3], bias},
+ *   fc.0.{weight [Z,16Z], bias}, fc.2.{weight, bias}, interpolate.{weight [16,n_frames], bias}, refine.0.{weight, bias},
+ *   refine.2.{weight, bias}; gradients are ACCUMULATED into dparams (null entries are skipped), dz is written.
+ *   uva_head_prenet_backward must follow a uva_head_prenet_forward(train = 1) on the same workspace. */
+int32_t uva_head_prenet_num_params(void);
+int uva_head_prenet_load_weights(UvaHead* h, const float* const* params, int32_t n_params, int32_t n_frames,
+                                 int32_t n_actions, void* stream);
+size_t uva_head_prenet_workspace_bytes(const UvaHead* h, int64_t B, int32_t train);
+int uva_head_prenet_forward(UvaHead* h, const float* z, int64_t B, float* out, void* ws, size_t ws_bytes, int32_t train,
+                            void* stream);
+int uva_head_prenet_backward(UvaHead* h, const float* dout, int64_t B, float* dz, float* const* dparams, void* ws,
+                             size_t ws_bytes, void* stream);
+
 /* Fused AdamW + EMA update of a list of fp32 parameter tensors in ONE pass.  Replaces
  * torch.optim.AdamW.step() as configured by the reference (policy/unified_video_action_policy.py:325-360:
  * decoupled weight decay, 0 on 1-D tensors and biases) followed by EMAModel.step()

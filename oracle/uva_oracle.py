@@ -494,6 +494,27 @@ def diffactloss_forward(P, S: Schedule, target, z, t, noise, emulate_bf16: bool 
     return training_losses(P, S, target, t, noise, z, emulate_bf16)["loss"].mean()
 
 
+def prenet_conv_fc(Pp, z, n_frames: int = 4, side: int = 16, emulate_bf16: bool = False):
+    """The "conv_fc" pre-net of DiffActLoss (DAL:41-61; forward DAL:112-124 == 169-181).  ``Pp``: the 12 pre-net
+    tensors under the reference's names (conv.0.*, fc.0.*, fc.2.*, interpolate.*, refine.0.*, refine.2.*).
+    z [B, n_frames * side * side, Z] -> [B, 16, Z].  ``emulate_bf16``: bf16-rounded GEMM operands with wide
+    accumulation at the points where the fused B200 pre-net rounds (conv / Linear inputs and weights)."""
+    B, S, Z = z.shape
+    r = (lambda t: _bf16r(t)) if emulate_bf16 else (lambda t: t)
+    x = z.reshape(B * n_frames, S // n_frames, Z)            # "b (t s) c -> (b t) s c"
+    x = x.reshape(B * n_frames, side, side, Z)               # "b (w h) c -> b w h c"
+    x = x.permute(0, 3, 1, 2)                                # "b w h c -> b c w h"
+    x = F.conv2d(r(x), r(Pp["conv.0.weight"]), Pp["conv.0.bias"], stride=1, padding=1)
+    x = F.adaptive_avg_pool2d(F.relu(x), (4, 4))
+    x = x.reshape(x.shape[0], -1)                            # "b c w h -> b (c w h)"
+    x = F.relu(F.linear(r(x), r(Pp["fc.0.weight"]), Pp["fc.0.bias"]))
+    x = F.linear(r(x), r(Pp["fc.2.weight"]), Pp["fc.2.bias"])
+    x = x.reshape(B, n_frames, Z).permute(0, 2, 1)           # "(b t) c -> b t c", permute(0, 2, 1)
+    x = F.linear(x, Pp["interpolate.weight"], Pp["interpolate.bias"]).permute(0, 2, 1)
+    x = F.relu(F.linear(r(x), r(Pp["refine.0.weight"]), Pp["refine.0.bias"]))
+    return F.linear(r(x), r(Pp["refine.2.weight"]), Pp["refine.2.bias"])
+
+
 def decoder_tail(x_dec, ln_w, ln_b, eps, temporal, spatial, skip: int = 0):
     """Tail of ``MAR.forward_mae_decoder`` (mar_con_unified.py:702-724): ``decoder_norm`` (nn.LayerNorm, eps 1e-6 for
     mar_base, MAR:1201), drop the ``skip`` leading text tokens (MAR:705-707), add the diffusion position embedding

@@ -211,3 +211,43 @@ def test_decoder_tail_restatement_vs_golden(golden_dir):
                        skip=int(g["meta"][4]))
     assert z.shape == g["z"].shape
     assert torch.equal(z, torch.from_numpy(g["z"]))
+
+
+PRENET_NAMES = ("conv.0.weight", "conv.0.bias", "fc.0.weight", "fc.0.bias", "fc.2.weight", "fc.2.bias",
+                "interpolate.weight", "interpolate.bias", "refine.0.weight", "refine.0.bias", "refine.2.weight", "refine.2.bias")
+
+
+def prenet_case(golden_dir):
+    """The seeded module / inputs of tests/golden/make_golden_prenet.py, rebuilt without the reference."""
+    from unified_video_action_b200 import DiffActLoss
+
+    g = np.load(os.path.join(golden_dir, "prenet.npz"))
+    seed, B = [int(v) for v in g["seed"]]
+    torch.manual_seed(seed)
+    mod = DiffActLoss(2, 768, 6, 1024, "100", n_frames=4, language_emb_model=None, language_emb_model_type=None)
+    sd = dict(mod.named_parameters())
+    for n in PRENET_NAMES:  # same constructor order as the reference => same weights from the same seed
+        f = sd[n].detach().double().flatten()
+        np.testing.assert_allclose([float(f.sum()), float(f.abs().sum()), float(f.norm())], g["wdigest." + n], rtol=1e-12)
+    gen = torch.Generator().manual_seed(seed + 1)
+    z = torch.randn(B, 1024, 768, generator=gen)
+    torch.rand(B, 16, 2, generator=gen)
+    cot = torch.randn(B, 16, 768, generator=gen)
+    return g, mod, z, cot
+
+
+def test_prenet_restatement_vs_reference_golden(golden_dir):
+    """oracle.prenet_conv_fc (DAL:112-124) against the unmodified reference's pre-net output, d z and parameter
+    gradients (tests/golden/prenet.npz): fp32, same ATen ops."""
+    g, mod, z, cot = prenet_case(golden_dir)
+    Pp = {n: p.detach().clone().requires_grad_(True) for n, p in mod.named_parameters() if n in PRENET_NAMES}
+    zz = z.clone().requires_grad_(True)
+    out = O.prenet_conv_fc(Pp, zz)
+    assert torch.equal(out.detach(), torch.from_numpy(g["out"]))
+    (out * cot).sum().backward()
+    np.testing.assert_allclose(zz.grad.flatten()[torch.from_numpy(g["dz_idx"])].numpy(), g["dz_val"], rtol=1e-5, atol=1e-8)
+    for n in PRENET_NAMES:
+        np.testing.assert_allclose(Pp[n].grad.flatten()[torch.from_numpy(g["gidx." + n])].numpy(), g["gval." + n], rtol=1e-4, atol=1e-7)
+    # the drop-in module's PyTorch pre-net (fp32 parity mode / CPU) is the same op sequence
+    with torch.no_grad():
+        assert torch.equal(mod.prenet_torch(z), torch.from_numpy(g["out"]))

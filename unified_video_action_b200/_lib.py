@@ -98,6 +98,8 @@ _lock = threading.Lock()
 SYMBOLS = [
     "uva_head_num_params", "uva_head_param_numel", "uva_head_create", "uva_head_destroy",
     "uva_schedule_table", "uva_head_load_weights", "uva_head_workspace_bytes", "uva_head_net_forward",
+    "uva_head_prenet_num_params", "uva_head_prenet_load_weights", "uva_head_prenet_workspace_bytes",
+    "uva_head_prenet_forward", "uva_head_prenet_backward",
     "uva_head_sample", "uva_head_sample_from_decoder", "uva_decoder_tail_rows", "uva_head_loss_fwd", "uva_head_loss_bwd", "uva_head_launch_count",
     "uva_gemm_bf16_selftest", "uva_last_error", "uva_build_info", "uva_head_timing_enable", "uva_head_timing_read",
     "uva_adamw_ema_step", "uva_nccl_version", "uva_nccl_unique_id", "uva_nccl_comm_create", "uva_nccl_comm_destroy",
@@ -135,6 +137,16 @@ def lib() -> ctypes.CDLL:
         L.uva_head_sample_from_decoder.restype = ctypes.c_int
         L.uva_head_sample_from_decoder.argtypes = [vp, vp, ctypes.POINTER(_Tail), vp, vp, vp, vp, vp, f32, f32, i32, i32, i32,
                                                    i64, vp, vp, ctypes.c_size_t, vp]
+        L.uva_head_prenet_num_params.restype = i32
+        L.uva_head_prenet_num_params.argtypes = []
+        L.uva_head_prenet_load_weights.restype = ctypes.c_int
+        L.uva_head_prenet_load_weights.argtypes = [vp, ctypes.POINTER(vp), i32, i32, i32, vp]
+        L.uva_head_prenet_workspace_bytes.restype = ctypes.c_size_t
+        L.uva_head_prenet_workspace_bytes.argtypes = [vp, i64, i32]
+        L.uva_head_prenet_forward.restype = ctypes.c_int
+        L.uva_head_prenet_forward.argtypes = [vp, vp, i64, vp, vp, ctypes.c_size_t, i32, vp]
+        L.uva_head_prenet_backward.restype = ctypes.c_int
+        L.uva_head_prenet_backward.argtypes = [vp, vp, i64, vp, ctypes.POINTER(vp), vp, ctypes.c_size_t, vp]
         L.uva_decoder_tail_rows.restype = ctypes.c_int
         L.uva_decoder_tail_rows.argtypes = [vp, ctypes.POINTER(_Tail), vp, i64, i32, vp, vp]
         L.uva_head_loss_fwd.restype = ctypes.c_int
@@ -354,6 +366,55 @@ class Head:
                                                   out.data_ptr(), ws.data_ptr(), ws.numel(), _stream()),
                "uva_head_sample_from_decoder")
         return (out, tr) if trace else out
+
+    # ---- fused DiffActLoss pre-net ----------------------------------------------------------
+    def prenet_load_weights(self, params: Sequence[torch.Tensor], n_frames: int, n_actions: int) -> None:
+        keep = [_f32c(p.detach(), "pre-net parameter") for p in params]
+        arr = (ctypes.c_void_p * len(keep))(*[p.data_ptr() for p in keep])
+        _check(lib().uva_head_prenet_load_weights(self._h, arr, len(keep), int(n_frames), int(n_actions), _stream()),
+               "uva_head_prenet_load_weights")
+        self.prenet_geom = (int(n_frames), int(n_actions))
+
+    def prenet_workspace(self, B: int, train: bool) -> torch.Tensor:
+        need = int(lib().uva_head_prenet_workspace_bytes(self._h, B, int(train)))
+        key = 2
+        ws = self._ws.get(key)
+        cur = torch.cuda.current_stream(self.device)
+        users = self._ws_streams.setdefault(key, {})
+        if ws is None or ws.numel() < need:
+            if ws is not None:
+                for st in users.values():
+                    ws.record_stream(st)
+            users.clear()
+            self._ws[key] = None
+            ws = self._ws[key] = torch.empty(max(need, 1024), dtype=torch.uint8, device=self.device)
+        users[cur.cuda_stream] = cur
+        return ws
+
+    def prenet_forward(self, z: torch.Tensor, train: bool = False) -> torch.Tensor:
+        """z [B, n_frames * 256, Z] -> [B, n_actions, Z] (DAL:112-124)."""
+        z = _f32c(z, "z")
+        B = z.shape[0]
+        T, J = self.prenet_geom
+        if z.dim() != 3 or z.shape[1] != T * 256 or z.shape[2] != self.Z:
+            raise RuntimeError(f"pre-net: z must be [B, {T * 256}, {self.Z}], got {tuple(z.shape)}")
+        out = torch.empty(B, J, self.Z, dtype=torch.float32, device=z.device)
+        ws = self.prenet_workspace(B, True) if train else self.prenet_workspace(B, False)
+        if train:
+            self.prenet_gen = getattr(self, "prenet_gen", 0) + 1
+        _check(lib().uva_head_prenet_forward(self._h, z.data_ptr(), B, out.data_ptr(), ws.data_ptr(), ws.numel(), int(train),
+                                             _stream()), "uva_head_prenet_forward")
+        return out
+
+    def prenet_backward(self, dout: torch.Tensor, B: int, dparams: Sequence[Optional[torch.Tensor]], want_dz: bool = True):
+        dout = _f32c(dout, "dout")
+        T, _ = self.prenet_geom
+        dz = torch.empty(B, T * 256, self.Z, dtype=torch.float32, device=dout.device) if want_dz else None
+        arr = (ctypes.c_void_p * len(dparams))(*[_ptr(g) for g in dparams])
+        ws = self.prenet_workspace(B, True)
+        _check(lib().uva_head_prenet_backward(self._h, dout.data_ptr(), B, _ptr(dz), arr, ws.data_ptr(), ws.numel(), _stream()),
+               "uva_head_prenet_backward")
+        return dz
 
     def loss_fwd(self, target, z, mask, t, noise, want_rows=False):
         target, z, noise = _f32c(target, "target"), _f32c(z, "z"), _f32c(noise, "noise")

@@ -28,6 +28,11 @@ struct EpiArgs {
   // EPI_DSILU_ACT on the CTA-pair kernel: column sums of the fp32 result (the bias gradient of the Linear in front of
   // the SiLU) are reduced over each warp's 32 rows with shuffles and added here with one atomic per column; null: off
   float* colsum = nullptr;
+  // deterministic split-K (single-CTA kernel, EPI_STORE_F32): split s of a tile stores its partial sums to row
+  // (row + s * split_rows) of `out`; the caller reduces the split_k partial planes in a fixed order afterwards
+  int32_t split_k = 0;
+  int64_t split_rows = 0;
+  int32_t conv_cpb = 0;  // implicit-GEMM convolution operands: 64-channel blocks per tap (C_in / 64)
   // LayerNorm-modulate pre-phase of the latency-path GEMM1 (umma_gemm_tn_kernel<.., EPI_SILU_ACT>, one wave, K = 1024):
   // before the main loop the CTAs of a 128-row panel produce the A operand a = LN(h) (1 + scale) + shift themselves
   // (a few rows each), meet at a panel barrier (pre_bar: {count, generation} per panel) and only then start their TMA
@@ -52,6 +57,10 @@ enum EpiKind {
   EPI_DSILU_ACT = 6,  // out(TA)[r,c]   = (acc) * SiLU'(aux(TA)[r,c])            (dgrad through SiLU)
   EPI_ATOMIC_F32 = 7, // atomicAdd(out(f32)[r,c], alpha * acc)                   (split-K wgrad)
   EPI_GATED_SAVE = 8, // q = acc + bias; out2(TA) = q; out(f32) = res + aux * q  (training fwd, DL:167)
+  EPI_RELU_ACT = 10,  // out(TA)[r,c]   = max(acc + bias, 0)                      (pre-net Linear + ReLU, DAL:47-55)
+  EPI_CONVPOOL = 11,  // CTA-pair kernel, implicit 3x3 convolution on 16 x 16 maps: y = max(acc + bias, 0); out2(TA) = y
+                      // (optional, for the backward), out(f32)[image][4x4 region][c] += y / 16   (Conv2d + ReLU +
+                      // AdaptiveAvgPool2d(4,4) of the DiffActLoss pre-net, DAL:41-46)
   EPI_LNMOD = 9,      // AdaLN GEMM with the LayerNorm-modulate fused (CTA-pair kernel only): tiles < ln_tiles
                       // hold 128 shift | 128 scale columns -> out(TA) = LN(res)[*ln_w+ln_b]*(1+scale)+shift;
                       // the other tiles (gate) are stored to out2(TA)                         (DL:93-94, 163-166)
@@ -68,6 +77,8 @@ struct Epi {
       reinterpret_cast<TA*>(e.out)[r * e.ldo + c] = from_f32<TA>(acc + b);
     } else if constexpr (KIND == EPI_SILU_ACT) {
       reinterpret_cast<TA*>(e.out)[r * e.ldo + c] = from_f32<TA>(silu_f(acc + b));
+    } else if constexpr (KIND == EPI_RELU_ACT) {
+      reinterpret_cast<TA*>(e.out)[r * e.ldo + c] = from_f32<TA>(fmaxf(acc + b, 0.f));
     } else if constexpr (KIND == EPI_GATED_RES || KIND == EPI_GATED_SAVE) {
       const float g = to_f32(reinterpret_cast<const TA*>(e.aux)[r * e.ldaux + c]);
       float* o = reinterpret_cast<float*>(e.out) + r * e.ldo + c;

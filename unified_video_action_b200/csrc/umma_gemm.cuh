@@ -164,6 +164,10 @@ struct RowEpi {
 #pragma unroll
         for (int j = 0; j < 32; ++j) x[j] = __fdividef(x[j], 1.0f + __expf(-x[j]));
       }
+      if constexpr (KIND == EPI_RELU_ACT) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) x[j] = fmaxf(x[j], 0.f);
+      }
       if constexpr (KIND == EPI_DSILU_ACT) {
         const uint4* ap = reinterpret_cast<const uint4*>(reinterpret_cast<const bf16*>(e.aux) + row * e.ldaux + col0);
 #pragma unroll
@@ -368,8 +372,9 @@ umma_gemm_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     for (int64_t item = blockIdx.x; item < num_tiles; item += gridDim.x) {
       int64_t m_blk; int n_blk;
       ug_tile_coords(item / splits, m_tiles, n_tiles, gm, m_blk, n_blk);
-      const int64_t row = m_blk * UG_BM + q * 32 + lane;
-      const bool row_ok = row < M;
+      const int64_t row_in = m_blk * UG_BM + q * 32 + lane;
+      const bool row_ok = row_in < M;
+      const int64_t row = row_in + (int64_t)(item % splits) * ep.split_rows;  // (split_rows = 0 unless partial planes are asked for)
       const int n0 = n_blk * BN + cg * kColsPerGroup;
       typename RowEpi<KIND, TA>::Pre pre;
       if (RowEpi<KIND, TA>::kNeedsPrefetch && row_ok) RowEpi<KIND, TA>::prefetch(ep, row, n0, pre);

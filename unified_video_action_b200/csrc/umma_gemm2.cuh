@@ -59,7 +59,13 @@ struct Umma2Cfg {
 // 64 of the 128 rows its half needs), so a CTA pulls 24 KB instead of 32 KB per k-block through the
 // L2 -> SMEM path, which is what bounds the CL = 2 kernel (profiles/r01_ncu_full_gemm2_v3_summary.txt).
 // The cluster size is a launch attribute (cudaLaunchAttributeClusterDimension).
-template <int BN, int KIND, typename TA, bool A_MN = false, bool B_MN = false, int CL = 2>
+// CONV (the DiffActLoss pre-net's Conv2d(C, C, 3, padding 1) on 16 x 16 maps as an implicit GEMM, NHWC bf16 input,
+// CL = 2 only):  1: the A operand is gathered - row m = pixel (image m / 256, w = (m % 256) / 16, h = m % 16),
+// k-block kb = (tap kb / cpb, channels 64 (kb % cpb) ..): one 4D TMA box {64 c, 16 h, 8 w, 1 image} at
+// (c0, kw - 1, w0 + kh - 1, image) per CTA, the padding is TMA's out-of-range zero fill (forward and, with the taps
+// flipped in the packed weight, data gradient).  2: the B operand (MN-major, weight-gradient form) is gathered the
+// same way: k = pixel, n = (tap, c_in), boxes {64 c, 16 h, 4 w, 1 image}.
+template <int BN, int KIND, typename TA, bool A_MN = false, bool B_MN = false, int CL = 2, int CONV = 0>
 __global__ void __launch_bounds__(UG_THREADS, 1)
 umma_gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                   const __grid_constant__ EpiMaps em, int64_t M, int N, int K, int gm, int splits, EpiArgs ep) {
@@ -160,13 +166,28 @@ umma_gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             const uint16_t mc = (uint16_t)(5u << rank);
             if constexpr (A_MN) tma_load_2d_2sm_mc(sa + pair * kAtomBytes, &tmA, &full_bar[stage], m0 + 64 * (int32_t)pair, kb * UG_BK, mc);
             else tma_load_2d_2sm_mc(sa + pair * kAtomBytes, &tmA, &full_bar[stage], kb * UG_BK, m0 + 64 * (int32_t)pair, mc);
+          } else if constexpr (CONV == 1) {
+            static_assert(CONV != 1 || (!A_MN && CL == 2), "conv gather of A: K-major, one pair per cluster");
+            const int tap = kb / ep.conv_cpb;
+            const int32_t c0 = (kb - tap * ep.conv_cpb) * UG_BK;
+            tma_load_4d_2sm(sa, &tmA, &full_bar[stage], c0, tap % 3 - 1, (int32_t)rank * 8 + tap / 3 - 1, (int32_t)m_blk);
           } else if constexpr (A_MN) {
 #pragma unroll
             for (int a = 0; a < UG_BM / 64; ++a) tma_load_2d_2sm(sa + a * kAtomBytes, &tmA, &full_bar[stage], m0 + 64 * a, kb * UG_BK);
           } else {
             tma_load_2d_2sm(sa, &tmA, &full_bar[stage], kb * UG_BK, m0);
           }
-          if constexpr (B_MN) {
+          if constexpr (CONV == 2) {
+            static_assert(CONV != 2 || (B_MN && CL == 2), "conv gather of B: MN-major, one pair per cluster");
+            const int cin = ep.conv_cpb * UG_BK;
+#pragma unroll
+            for (int a = 0; a < Cfg::kBNH / 64; ++a) {
+              const int nidx = n0 + 64 * a;  // = tap * C_in + c_in
+              const int tap = nidx / cin;
+              tma_load_4d_2sm(sb + a * kAtomBytes, &tmB, &full_bar[stage], nidx - tap * cin, tap % 3 - 1,
+                              (kb & 3) * 4 + tap / 3 - 1, kb >> 2);
+            }
+          } else if constexpr (B_MN) {
 #pragma unroll
             for (int a = 0; a < Cfg::kBNH / 64; ++a) tma_load_2d_2sm(sb + a * kAtomBytes, &tmB, &full_bar[stage], n0 + 64 * a, kb * UG_BK);
           } else {
@@ -609,6 +630,46 @@ umma_gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           fence_proxy_async();
           named_bar_sync(1 + cg, 128);
           if (q == 0 && lane == 0) mbar_arrive(&sready_bar[slot]);  // hand the box to the store thread (warp 2)
+        }
+      } else if constexpr (KIND == EPI_CONVPOOL) {
+        // y = max(acc + bias, 0) per pixel (row) and channel; 4 x 4 average pool: this CTA's 128 rows are 8 w-rows x 16 h
+        // of one image, warp q holds w = 2q, 2q + 1 (lane >> 4) and h = lane & 15, so a pool region is the 8 lanes with
+        // the same (lane >> 2) & 3 of TWO warps: three shuffle steps (lane bits 0, 1, 4), then one atomic per channel
+        // from lanes 0, 4, 8, 12 (the two warps of a region meet in the atomics)
+        const int64_t img = m_blk;
+        const int region0 = ((int)rank * 2 + (q >> 1)) * 4;  // pool row (w / 4) * 4
+        mbar_wait(&tfull_bar[acc], acc_phase);
+        tc_fence_after();
+#pragma unroll 1
+        for (int c0 = 0; c0 < kColsPerGroup; c0 += 32) {
+          uint32_t v[32];
+          tmem_ld_32x32(t_tile + (uint32_t)(cg * kColsPerGroup + c0), v);
+          float b[32];
+          bias32_ldg(ep.bias + n0 + c0, b);
+          tmem_ld_wait();
+          float y[32];
+#pragma unroll
+          for (int i = 0; i < 32; ++i) y[i] = fmaxf(__uint_as_float(v[i]) + b[i], 0.f);
+          if (ep.out2 != nullptr) {  // kept for the backward (its sign is the ReLU mask)
+            uint4* o2 = reinterpret_cast<uint4*>(reinterpret_cast<bf16*>(ep.out2) + row * ep.ldo2 + n0 + c0);
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+              o2[i] = make_uint4(pack_bf16x2(y[8 * i], y[8 * i + 1]), pack_bf16x2(y[8 * i + 2], y[8 * i + 3]),
+                                 pack_bf16x2(y[8 * i + 4], y[8 * i + 5]), pack_bf16x2(y[8 * i + 6], y[8 * i + 7]));
+          }
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            float t = y[i];
+            t += __shfl_xor_sync(0xffffffffu, t, 1);
+            t += __shfl_xor_sync(0xffffffffu, t, 2);
+            t += __shfl_xor_sync(0xffffffffu, t, 16);
+            y[i] = t;
+          }
+          if ((lane & 0x13) == 0) {
+            float* o = reinterpret_cast<float*>(ep.out) + (img * 16 + region0 + (lane >> 2)) * (int64_t)ep.ldo + n0 + c0;
+#pragma unroll
+            for (int i = 0; i < 32; ++i) atomicAdd(o + i, y[i] * 0.0625f);
+          }
         }
       } else {
         typename RowEpi<KIND, TA>::Pre pre;

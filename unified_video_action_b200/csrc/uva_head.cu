@@ -25,6 +25,7 @@
 #include "chain_kernel.cuh"
 #include "final_ddpm.cuh"
 #include "optim.cuh"
+#include "prenet_kernels.cuh"
 
 using namespace uva;
 
@@ -138,6 +139,8 @@ struct DevTables {  // fp32 device copies of one process' tables, [T] each
         *coef1 = nullptr, *coef2 = nullptr, *post_logvar = nullptr, *log_beta = nullptr;
 };
 
+struct UvaPrenet;
+static void prenet_free(UvaPrenet* p);
 static const int kLnPrePanels = 64;  // 128-row panels the LayerNorm pre-phase barriers cover (latency path: <= small_rows / 128)
 struct UvaHead {
   UvaHeadDesc d;
@@ -168,6 +171,7 @@ struct UvaHead {
   float* adab_p = nullptr;                // [nmod] bias in the same order
   std::vector<size_t> ob_w1, ob_w2;       // [W,W]
   bool weights_loaded = false;
+  UvaPrenet* prenet = nullptr;  // fused DiffActLoss pre-net (head_prenet.inc), allocated by uva_head_prenet_load_weights
   int64_t launches = 0;
   PFN_encodeTiled encode = nullptr;
   // optional per-category GEMM timing (bench.py roofline): CUDA event pairs on the launch stream
@@ -506,6 +510,7 @@ extern "C" void uva_head_destroy(UvaHead* h) {
     if (g.exec) cudaGraphExecDestroy(g.exec);
   for (auto& g : h->tgraphs)
     if (g.exec) cudaGraphExecDestroy(g.exec);
+  prenet_free(h->prenet);
   if (h->side) cudaStreamDestroy(h->side);
   if (h->ev_fork) cudaEventDestroy(h->ev_fork);
   if (h->ev_join) cudaEventDestroy(h->ev_join);
@@ -562,4 +567,5 @@ extern "C" int uva_adamw_ema_step(int32_t n_tensors, float* const* params, const
 #include "head_small.inc"
 #include "head_sample.inc"
 #include "head_train.inc"
+#include "head_prenet.inc"
 #include "collective.inc"

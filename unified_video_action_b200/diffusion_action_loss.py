@@ -15,11 +15,43 @@ from typing import Optional
 import torch
 import torch.nn as nn
 
-from .diffusion_loss import _ENTRY, SimpleMLPAdaLN, _FusedLoss, _require_cuda, sample_rows
+from . import _lib
+from .diffusion_loss import _ENTRY, SimpleMLPAdaLN, _FusedLoss, _grad_buffers, _require_cuda, sample_rows
 
 _SIDE_STREAMS: dict = {}  # device index -> high-priority stream shared by the action heads of that device
 _PRENET_GRAPHS: dict = {}  # id(module) -> (key, CUDAGraph, static input, static output); see DiffActLoss._prenet_replay
 PRENET_GRAPH_MAX_BATCH = 8  # latency regime only: larger batches are bound by the convolution itself, not by launches
+
+
+PRENET_PARAMS = ("conv.0.weight", "conv.0.bias", "fc.0.weight", "fc.0.bias", "fc.2.weight", "fc.2.bias",
+                 "interpolate.weight", "interpolate.bias", "refine.0.weight", "refine.0.bias", "refine.2.weight", "refine.2.bias")
+
+
+class _FusedPrenet(torch.autograd.Function):
+    """The "conv_fc" pre-net (DAL:112-124) as one op of the CUDA library: implicit-GEMM convolution
+    with the ReLU + 4 x 4 average pool in its epilogue, tcgen05 Linears; hand-written backward on the same cores."""
+
+    @staticmethod
+    def forward(ctx, mod, z, *params):
+        head = mod._prenet_head()
+        train = any(ctx.needs_input_grad)  # (grad mode itself is off inside Function.forward)
+        out = head.prenet_forward(z, train=train)
+        ctx.mod, ctx.B, ctx.z_dtype = mod, z.shape[0], z.dtype
+        ctx.gen = getattr(head, "prenet_gen", 0)
+        ctx.save_for_backward(z)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        mod = ctx.mod
+        (z,) = ctx.saved_tensors
+        head = mod._prenet_head()
+        if getattr(head, "prenet_gen", 0) != ctx.gen:  # another training forward overwrote the kept activations: redo ours
+            head.prenet_forward(z, train=True)
+        params = mod._prenet_params()
+        flat, grads = _grad_buffers(params, dout.device)
+        dz = head.prenet_backward(dout, ctx.B, grads, want_dz=ctx.needs_input_grad[1])
+        return (None, dz.to(ctx.z_dtype) if dz is not None else None, *grads)
 
 
 class DiffActLoss(nn.Module):
@@ -76,8 +108,40 @@ class DiffActLoss(nn.Module):
             precision=kwargs.get("precision"), T_train=self.num_timesteps, T_gen=self.num_sampling_steps,
         )
 
+    # ---- fused pre-net ------------------------------------------------------------------------------------
+    def _prenet_params(self):
+        cached = self.__dict__.get("_pn_params")
+        if cached is not None and cached[0] is self.conv[0].weight and cached[-1] is self.refine[2].bias:
+            return cached
+        d = dict(self.named_parameters())
+        cached = self.__dict__["_pn_params"] = [d[n] for n in PRENET_PARAMS]
+        return cached
+
+    def _prenet_head(self) -> "_lib.Head":
+        """The action head's library handle with up-to-date packed pre-net operands."""
+        params = self._prenet_params()
+        with torch.cuda.device(params[0].device):
+            head = self.net.head()
+            key = (id(head),) + tuple((p.data_ptr(), p._version) for p in params)
+            if key != self.__dict__.get("_pn_key"):
+                head.prenet_load_weights(params, self.num_frames, self.num_actions)
+                self.__dict__["_pn_key"] = key
+        return head
+
+    def _fused_prenet_ok(self, z: torch.Tensor) -> bool:
+        return (self.act_model_type == "conv_fc" and z.is_cuda and z.dim() == 3 and z.shape[1] == self.num_frames * self.w * self.h
+                and self.net._mode == _lib.MODE_BF16 and z.shape[2] % 256 == 0 and self.n_frames == self.num_frames
+                and os.environ.get("UVA_FUSED_PRENET", "1") != "0")
+
     def prenet(self, z: torch.Tensor) -> torch.Tensor:
-        """z [B, 1024, Z] -> [B, 16, Z]  (DAL:112-143 == DAL:169-200)."""
+        """z [B, 1024, Z] -> [B, 16, Z]  (DAL:112-143 == DAL:169-200).  bf16 mode on CUDA: the fused library pre-net
+        (``UVA_FUSED_PRENET=0`` or the fp32 parity mode: the PyTorch modules below, the reference's own op sequence)."""
+        if self._fused_prenet_ok(z):
+            with torch.cuda.device(z.device):
+                return _FusedPrenet.apply(self, z, *self._prenet_params())
+        return self.prenet_torch(z)
+
+    def prenet_torch(self, z: torch.Tensor) -> torch.Tensor:
         if self.act_model_type == "conv_fc":
             B, S, Cz = z.shape
             s = S // self.n_frames

@@ -103,3 +103,5 @@ class HeadAdamW:
             for sub in m.modules():
                 if hasattr(sub, "_packed_key"):
                     sub._packed_key = None
+                if "_pn_key" in sub.__dict__:  # packed operands of the fused DiffActLoss pre-net
+                    sub.__dict__["_pn_key"] = None
