@@ -597,6 +597,7 @@ def test_prenet_graph_replay_equals_eager(monkeypatch):
     from unified_video_action_b200.diffusion_action_loss import _PRENET_GRAPHS
 
     monkeypatch.setenv("UVA_PRENET_GRAPH", "1")  # opt-in switch
+    monkeypatch.setenv("UVA_FUSED_PRENET", "0")  # ... of the PyTorch pre-net (the fused library pre-net needs no replay)
     torch.manual_seed(3)
     act = DiffActLoss(2, 768, 6, 1024, "100", n_frames=4, language_emb_model=None, language_emb_model_type=None).to(dev)
     with torch.no_grad():

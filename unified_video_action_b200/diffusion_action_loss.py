@@ -174,6 +174,8 @@ class DiffActLoss(nn.Module):
         (optimizer steps, load_state_dict) are seen; anything that moves them (``.to()``, a dtype cast), another
         shape or another autocast state re-captures.  The returned tensor is the graph's static output: valid
         until the next call on this module (``sample`` consumes it at once on the same stream)."""
+        if self._fused_prenet_ok(z):  # the library pre-net is a handful of launches already: nothing to replay
+            return self.prenet(z)
         if (not z.is_cuda or z.shape[0] > PRENET_GRAPH_MAX_BATCH or torch.is_grad_enabled()
                 or os.environ.get("UVA_PRENET_GRAPH", "0") == "0" or torch.cuda.is_current_stream_capturing()):
             return self.prenet(z)
