@@ -1,9 +1,7 @@
 set -u
 mkdir -p gpurun_out
-timeout 1500 python -m pytest tests -m gpu -x -q > gpurun_out/r02n_tests.log 2>&1; echo "rc=$?"; tail -n 3 gpurun_out/r02n_tests.log
-for f in 1 0; do
-UVA_FUSED_PRENET=$f timeout 600 python bench.py --workload latency > gpurun_out/r02n_lat_f$f.json 2> gpurun_out/r02n_lat_f$f.err; python -c "
-import json; d=json.load(open('gpurun_out/r02n_lat_f$f.json'))['detail']; print('fused=$f', {k:(round(v['p50_ms'],3), round(v['p50_ms_device_noise'],3)) for k,v in d.items()})"; tail -n 2 gpurun_out/r02n_lat_f$f.err
-UVA_FUSED_PRENET=$f timeout 600 python bench.py --workload train --steps 20 --warmup 5 > gpurun_out/r02n_train_f$f.json 2> gpurun_out/r02n_train_f$f.err; python -c "
-import json; d=json.load(open('gpurun_out/r02n_train_f$f.json')); print('fused=$f train', d['ms_per_step'], d['detail']['p50_ms'], d['detail']['max_ms'])"; tail -n 2 gpurun_out/r02n_train_f$f.err
+for v in 0 1 0 1; do
+UVA_ZIGZAG=$v timeout 600 python bench.py --steps 2 --warmup 2 --no-extras --no-cpu-baseline > gpurun_out/r02s_bench_z$v.json 2> gpurun_out/r02s_bench_z$v.err; echo "zigzag $v rc=$?"; python -c "
+import json; d=json.load(open('gpurun_out/r02s_bench_z$v.json')); print(d['value'], d['ms_per_step'], d['step_frac_of_burst_peak'], d['clocks'])"; tail -n 2 gpurun_out/r02s_bench_z$v.err
 done
+timeout 900 python -m pytest tests/test_gpu_headline.py tests/test_gpu_infer.py -x -q > gpurun_out/r02s_tests.log 2>&1; echo "rc=$?"; tail -n 3 gpurun_out/r02s_tests.log
