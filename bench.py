@@ -263,7 +263,7 @@ def measure_train(dev, world, B=16, iters=5, warmup=2, bf16_wire=False):
     if world > 1 and os.environ.get("UVA_EARLY_ALLREDUCE", "1") != "0":
         from unified_video_action_b200 import overlap_allreduce
 
-        overlap_allreduce([vid, act], bf16=bf16_wire)  # each head's all-reduce starts when its own gradients are in place
+        overlap_allreduce([vid, act], bf16=bf16_wire, in_backward=os.environ.get("UVA_IN_BACKWARD", "0") != "0")  # collectives start while the backward runs
     g = torch.Generator(device=dev).manual_seed(4321)
     z = torch.randn(B, 1024, Z, generator=g, device=dev, requires_grad=True)
     target = 0.2325 * torch.randn(B, 1024, C, generator=g, device=dev)

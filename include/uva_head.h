@@ -224,6 +224,14 @@ int uva_nccl_comm_create(int32_t world_size, int32_t rank, const void* id128 /*h
 int uva_nccl_comm_destroy(void* comm);
 int uva_head_allreduce_grads(void* comm, float* flat, int64_t count, int32_t average, void* stream);
 int uva_head_allreduce_grads_bf16(void* comm, float* flat, void* scratch, int64_t count, int32_t average, void* stream);
+/* The same collective from INSIDE the backward: while a communicator is set, uva_head_loss_bwd (calls with more than
+ * 1024 rows) all-reduces every contiguous range of the caller's flat gradient buffer on `comm_stream` as soon as the
+ * kernels that write it are enqueued (final linear, each block's in_ln + MLP, each adaLN Linear, the embedders:
+ * 3 * depth + 3 collectives), so that the all-reduce runs behind the rest of the backward instead of after it.  The
+ * gradient tensors of such a range must be one contiguous span (gaps <= 3 floats, zero-filled).  comm == NULL: off.
+ * uva_head_grad_sync_launched: collectives the last loss_bwd enqueued (0: small batch, reduce afterwards). */
+int uva_head_set_grad_sync(UvaHead* h, void* comm, void* comm_stream, int32_t average);
+int32_t uva_head_grad_sync_launched(const UvaHead* h);
 
 /* Joint training step (MAR:770-784): the video head (16 384 rows) and the action head (256 rows) are independent
  * and run on two streams.  The video head's persistent GEMM grids would take every SM, so the small head could

@@ -129,6 +129,34 @@ def _worker(rank, world, port, out_dir):
         for k, p in head.net.named_parameters():
             scale = float(want[k].abs().max())
             assert float((p.grad - want[k]).abs().max()) <= 1e-2 * max(scale, 1e-30), ("bf16 wire", k)
+        # a batch above the small-batch limit: the library reduces the gradient ranges from INSIDE loss_bwd
+        # (uva_head_set_grad_sync: 3 * depth + 3 collectives on the communicator's stream, behind the running backward)
+        gen = torch.Generator().manual_seed(200 + rank)
+        B2, S2 = 2, 640
+        target2 = torch.randn(B2, S2, 16, generator=gen).to(dev)
+        z2 = torch.randn(B2, S2, 768, generator=gen).to(dev).requires_grad_(True)
+        mask2 = (torch.rand(B2, S2, generator=gen) > 0.2).float().to(dev)
+        overlap_allreduce([head], in_backward=False)
+        for p in head.net.parameters():
+            p.grad = None
+        torch.manual_seed(17 + rank)
+        head(target2, z2, mask2).backward()
+        allreduce_head_grads([head])
+        torch.cuda.synchronize()
+        want2 = {k: p.grad.clone() for k, p in head.net.named_parameters()}
+        overlap_allreduce([head], in_backward=True)
+        for rep in range(2):
+            for p in head.net.parameters():
+                p.grad = None
+            torch.manual_seed(17 + rank)
+            head(target2, z2, mask2).backward()
+            sync = head.net._grad_sync
+            assert sync.pending is not None and sync.strict, "the in-backward collectives did not start"
+            assert allreduce_head_grads([head]) == 1
+            torch.cuda.synchronize()
+            for k, p in head.net.named_parameters():
+                scale = float(want2[k].abs().max())
+                assert float((p.grad - want2[k]).abs().max()) <= 2e-5 * max(scale, 1e-30), ("in-backward", rep, k)
         open(os.path.join(out_dir, f"ok{rank}"), "w").write("ok")
     finally:
         dist.destroy_process_group()

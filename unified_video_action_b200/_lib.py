@@ -103,7 +103,7 @@ SYMBOLS = [
     "uva_head_sample", "uva_head_sample_from_decoder", "uva_decoder_tail_rows", "uva_head_loss_fwd", "uva_head_loss_bwd", "uva_head_launch_count",
     "uva_gemm_bf16_selftest", "uva_last_error", "uva_build_info", "uva_head_timing_enable", "uva_head_timing_read",
     "uva_adamw_ema_step", "uva_nccl_version", "uva_nccl_unique_id", "uva_nccl_comm_create", "uva_nccl_comm_destroy",
-    "uva_head_allreduce_grads", "uva_head_allreduce_grads_bf16", "uva_head_set_noise_seed", "uva_philox_normal", "uva_head_set_train_reserve",
+    "uva_head_allreduce_grads", "uva_head_allreduce_grads_bf16", "uva_head_set_grad_sync", "uva_head_grad_sync_launched", "uva_head_set_noise_seed", "uva_philox_normal", "uva_head_set_train_reserve",
 ]
 
 
@@ -179,6 +179,10 @@ def lib() -> ctypes.CDLL:
         L.uva_nccl_comm_destroy.argtypes = [vp]
         L.uva_head_allreduce_grads.restype = ctypes.c_int
         L.uva_head_allreduce_grads.argtypes = [vp, vp, i64, i32, vp]
+        L.uva_head_set_grad_sync.restype = ctypes.c_int
+        L.uva_head_set_grad_sync.argtypes = [vp, vp, vp, i32]
+        L.uva_head_grad_sync_launched.restype = i32
+        L.uva_head_grad_sync_launched.argtypes = [vp]
         L.uva_head_allreduce_grads_bf16.restype = ctypes.c_int
         L.uva_head_allreduce_grads_bf16.argtypes = [vp, vp, vp, i64, i32, vp]
         L.uva_last_error.restype = ctypes.c_char_p
@@ -267,6 +271,18 @@ class Head:
             self._ws[what] = ws
         users[cur.cuda_stream] = cur
         return ws
+
+    def set_grad_sync(self, comm: Optional["GradComm"], average: bool = True) -> None:
+        """While set, ``loss_bwd`` all-reduces ranges of the flat gradient buffer on the communicator's stream as it
+        goes (``uva_head_set_grad_sync``); ``None`` turns it off."""
+        if comm is None:
+            _check(lib().uva_head_set_grad_sync(self._h, None, None, 1), "uva_head_set_grad_sync")
+        else:
+            _check(lib().uva_head_set_grad_sync(self._h, comm._c, comm.stream(self.device).cuda_stream, int(average)),
+                   "uva_head_set_grad_sync")
+
+    def grad_sync_launched(self) -> int:
+        return int(lib().uva_head_grad_sync_launched(self._h))
 
     def set_train_reserve(self, sms: int) -> None:
         _check(lib().uva_head_set_train_reserve(self._h, int(sms)), "uva_head_set_train_reserve")
@@ -496,13 +512,18 @@ class GradComm:
         self._c = c
         self.device = torch.device("cuda", torch.cuda.current_device())
 
+    def stream(self, dev) -> "torch.cuda.Stream":
+        """The one stream all collectives of this communicator run on (same order on every rank)."""
+        if getattr(self, "_stream", None) is None:
+            self._stream = torch.cuda.Stream(device=dev, priority=-1)
+        return self._stream
+
     def all_reduce_async(self, flat: torch.Tensor, average: bool = True, bf16: bool = False) -> "torch.cuda.Event":
         """The same collective on this communicator's own stream, behind everything already enqueued on the
         caller's stream; returns the event a consumer of ``flat`` has to wait for.  All collectives of one
         communicator go through this one stream, so they keep one order on every rank."""
         dev = flat.device
-        if getattr(self, "_stream", None) is None:
-            self._stream = torch.cuda.Stream(device=dev, priority=-1)
+        self.stream(dev)
         self._stream.wait_event(torch.cuda.current_stream(dev).record_event())
         with torch.cuda.stream(self._stream):
             self.all_reduce_(flat, average, bf16=bf16)

@@ -171,6 +171,11 @@ struct UvaHead {
   float* adab_p = nullptr;                // [nmod] bias in the same order
   std::vector<size_t> ob_w1, ob_w2;       // [W,W]
   bool weights_loaded = false;
+  // Data-parallel training: while set (uva_head_set_grad_sync), loss_bwd all-reduces every contiguous range of the
+  // caller's flat gradient buffer on the communicator's stream as soon as the kernels that write it are enqueued
+  // (final layer, each block's MLP part, each AdaLN Linear, the embedders) - the collective hides behind the rest
+  // of the backward instead of following it (collective.inc)
+  struct GradSync { void* comm = nullptr; cudaStream_t cs = nullptr; int average = 1; int launched = 0; std::vector<cudaEvent_t> ev; } gsync;
   UvaPrenet* prenet = nullptr;  // fused DiffActLoss pre-net (head_prenet.inc), allocated by uva_head_prenet_load_weights
   int64_t launches = 0;
   PFN_encodeTiled encode = nullptr;
@@ -510,6 +515,7 @@ extern "C" void uva_head_destroy(UvaHead* h) {
     if (g.exec) cudaGraphExecDestroy(g.exec);
   for (auto& g : h->tgraphs)
     if (g.exec) cudaGraphExecDestroy(g.exec);
+  for (auto e : h->gsync.ev) cudaEventDestroy(e);
   prenet_free(h->prenet);
   if (h->side) cudaStreamDestroy(h->side);
   if (h->ev_fork) cudaEventDestroy(h->ev_fork);
@@ -566,6 +572,6 @@ extern "C" int uva_adamw_ema_step(int32_t n_tensors, float* const* params, const
 #include "head_infer.inc"
 #include "head_small.inc"
 #include "head_sample.inc"
+#include "collective.inc"
 #include "head_train.inc"
 #include "head_prenet.inc"
-#include "collective.inc"

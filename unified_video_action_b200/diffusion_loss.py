@@ -277,7 +277,26 @@ class _FusedLoss(torch.autograd.Function):
                 # the reference's autograd gives - instead of differentiating the wrong forward.
                 head.loss_fwd(target, z, mask if ctx.has_mask else None, t, noise)
             flat, grads = _grad_buffers(params, z.device)
-            dz = head.loss_bwd(dloss.float(), target, z, mask if ctx.has_mask else None, t, noise, grads)
+            sync = getattr(net, "_grad_sync", None)
+            # data-parallel training: let the library all-reduce the gradient ranges while the backward is still running
+            # (uva_head_set_grad_sync).  Only when autograd is sure to adopt the views of `flat` as .grad: nothing to
+            # accumulate into, no tensor hooks, no double backward.
+            inb = (sync is not None and sync.in_backward and not torch.is_grad_enabled()
+                   and all(p.grad is None and not p._backward_hooks for p in params if p.requires_grad))
+            if inb:
+                if sync.pending is not None:  # an unconsumed collective of an earlier backward: not this path
+                    inb = False
+                else:
+                    head.set_grad_sync(sync.comm(z.device), sync.average)
+            try:
+                dz = head.loss_bwd(dloss.float(), target, z, mask if ctx.has_mask else None, t, noise, grads)
+            finally:
+                if inb:
+                    launched = head.grad_sync_launched()
+                    head.set_grad_sync(None)
+            if inb and launched > 0:
+                sync.launched_in_backward(flat)
+                return (None, None, dz.to(ctx.z_dtype) if ctx.needs_input_grad[2] else None, None, None, None, *grads)
         sync = getattr(net, "_grad_sync", None)
         if sync is not None:
             # data-parallel training (patch.overlap_allreduce): the head's gradients are complete here, long before

@@ -136,8 +136,12 @@ class _GradSync:
     new gradients into the buffer that collective is still rewriting - and forgotten, so that
     ``allreduce_head_grads`` reduces the accumulated sum in full."""
 
-    def __init__(self, group, average: bool, bf16: bool = False):
+    def __init__(self, group, average: bool, bf16: bool = False, in_backward: bool = False):
         self.group, self.average, self.bf16 = group, average, bf16
+        # the library reduces gradient ranges from inside loss_bwd (fp32 wire only): the collective hides behind the
+        # rest of the backward; see _FusedLoss.backward for when it applies
+        self.in_backward = in_backward and not bf16
+        self.strict = False  # set when a collective was launched before autograd had adopted the gradient views
         self.pending = None   # (flat, _Done) of the collective in flight
         self.armed = None     # flat buffer of the backward whose AccumulateGrad nodes are running now
         self.count = self.need = 0
@@ -159,6 +163,14 @@ class _GradSync:
             self.pending = None
         self.armed, self.count, self.params = flat, 0, params
         self.need = sum(1 for p in params if p.requires_grad)
+
+    def launched_in_backward(self, flat: torch.Tensor) -> None:
+        """loss_bwd enqueued the range collectives itself: remember the buffer and the point of the communicator's
+        stream a consumer has to wait for."""
+        cs = self.comm(flat.device).stream(flat.device)
+        flat.record_stream(cs)
+        self.pending = (flat, _Done(event=cs.record_event()))
+        self.armed, self.strict = None, True
 
     def hook(self, _param) -> None:
         if self.armed is None:
@@ -182,13 +194,22 @@ class _GradSync:
         self.pending = (flat, _Done(work=dist.all_reduce(flat, group=self.group, async_op=True)))
 
 
-def overlap_allreduce(heads: Iterable[nn.Module], group=None, average: bool = True, bf16: bool = False) -> None:
+def overlap_allreduce(heads: Iterable[nn.Module], group=None, average: bool = True, bf16: bool = False,
+                      in_backward: bool = False) -> None:
     """Start each head's gradient all-reduce as soon as its gradients are in place ("issued from the
     extension when the last wgrad tile lands, overlapped with the backbone's backward"): the fused backward of a
     head ends long before the MAR decoder / encoder backward does, so the collective runs on the communicator's own
     stream beside it.  ``allreduce_head_grads`` afterwards only waits for those collectives (and reduces what else
     the head owns, e.g. the PyTorch pre-net).  ``bf16``: the flat buffer crosses NVLink as bf16 (71.5 MB per head
-    instead of 143 MB; converted on both sides by the library).  Needs the process group to be initialised;
+    instead of 143 MB; converted on both sides by the library).  ``in_backward`` (fp32 wire): large heads are reduced
+    range by range from INSIDE their fused backward (final layer, every block, every adaLN Linear, the embedders:
+    3 * depth + 3 collectives, each started as soon as its gradients are enqueued), so the collective also hides behind
+    the head's own backward; falls back to the hook-based start when gradients accumulate into existing ``.grad``, a
+    parameter has tensor hooks or the batch is small.  Off by default: measured on 2 B200s it buys nothing in the
+    head-only step (6.09 vs 6.02 ms p50; 1 GPU 5.5 ms) - the head's persistent GEMM grids fill every SM, NCCL's CTAs
+    cannot co-reside with them and the collective ends up in the gaps either way; with fewer NCCL channels
+    (NCCL_MAX_NCHANNELS 8 / 4 / 2: 6.5 / 8.4 / 12.4 ms) it only gets longer.  It is meant for a full training step,
+    where the backbone's backward follows the heads'.  Needs the process group to be initialised;
     ``None`` heads or ``heads=[]`` are fine.  Call once after ``patch()``; calling it again replaces the hooks."""
     for head in heads:
         net = getattr(head, "net", None)
@@ -198,7 +219,7 @@ def overlap_allreduce(heads: Iterable[nn.Module], group=None, average: bool = Tr
         if old is not None:
             for hd in old.handles:
                 hd.remove()
-        sync = net._grad_sync = _GradSync(group, average, bf16)
+        sync = net._grad_sync = _GradSync(group, average, bf16, in_backward)
         for p in net.parameters():
             sync.handles.append(p.register_post_accumulate_grad_hook(sync.hook))
 
@@ -230,7 +251,12 @@ def allreduce_head_grads(heads: Iterable[nn.Module], group=None, average: bool =
             sync.pending = None
             done.wait(flat0.device)  # always: nothing below may touch the buffer while the collective rewrites it
             if groups.pop(flat0.untyped_storage().data_ptr(), None) is not None:
-                n += 1  # .grad are views of the reduced buffer (checked when the collective was launched)
+                n += 1  # .grad are views of the reduced buffer
+            elif sync.strict:
+                raise RuntimeError("the head's gradients were all-reduced from inside its backward, but autograd did not keep "
+                                   "the library's gradient buffer as .grad (cloned gradients would be torn): call "
+                                   "overlap_allreduce(heads, in_backward=False)")
+            sync.strict = False
         loose = []
         for members in groups.values():
             flat = _shared_flat(members) if len(members) > 1 else None
