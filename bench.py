@@ -45,7 +45,7 @@ FLOP_PER_ROW_STEP = 2 * (C * W + DEPTH * 5 * W * W + 2 * W * W + W * 2 * C)  # 6
 ADA_FLOP_PER_ROW = 2 * (3 * DEPTH + 2) * W * W  # AdaLN modulation GEMM, per row per denoise step
 # dram__bytes_read.sum + dram__bytes_write.sum of one EPI_LNMOD launch (65536 rows x 3072 columns) from the
 # ncu --set full capture in profiles/ (None until captured for the current kernel)
-NCU_TRAFFIC_BYTES = 654.9e6  # profiles/r01_ncu_full_v7_summary.txt: 414.0 MB read + 240.9 MB written
+NCU_TRAFFIC_BYTES = 653.3e6  # profiles/r02_ncu_full_summary.txt: 413.2 MB read + 240.1 MB written (r01: 654.9e6)
 TRAIN_FLOP_PER_ROW = 6 * (C * W + 256 * W + W * W + Z * W + DEPTH * 5 * W * W + 2 * W * W + W * 2 * C)
 
 
