@@ -140,7 +140,9 @@ __device__ __forceinline__ void sk_wait_done(const unsigned int* p, unsigned int
     unsigned int v;
     asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     if (v >= target) return;
+#if !(defined(UVA_DEBUG) && defined(UVA_EXP_SK_NO_SLEEP))
     __nanosleep(40);
+#endif
     if ((++spins & 0xFFu) == 0) {
       const uint64_t now = global_timer_ns();
       if (t0 == 0) t0 = now;
@@ -304,7 +306,11 @@ umma_stack_kernel(const __grid_constant__ StackMaps tm, const __grid_constant__ 
         }
         bulk_wait_read<0>();
         mbar_arrive(&eempty_bar[prev_slot]);
+#if defined(UVA_DEBUG) && defined(UVA_EXP_SK_NO_COMPLETION)  // timing experiment only (results may be wrong)
+        (void)0;
+#else
         bulk_wait_all();  // this CTA's half of the item is in memory
+#endif
         sk_signal(sa.done + (int64_t)it.layer * m_tiles + it.m);
       }
     }
