@@ -331,7 +331,7 @@ def measure_train(dev, world, B=16, iters=5, warmup=2, bf16_wire=False):
             "tflops_per_gpu": (B * 1024) * TRAIN_FLOP_PER_ROW / (ms / 1e3) / 1e12, "loss": float(loss.detach()),
             "collective": ("none (1 GPU)" if world == 1 else
                            f"NCCL all-reduce of the head gradients only (2 flat buffers, {'bf16' if bf16_wire else 'fp32'} on the wire), started from each head's backward"),
-            "what": f"DiffLoss fwd+bwd {B}x1024 rows + DiffActLoss fwd+bwd {B}x16 rows (incl. its PyTorch pre-net), bf16"}
+            "what": f"DiffLoss fwd+bwd {B}x1024 rows + DiffActLoss fwd+bwd {B}x16 rows (incl. its conv_fc pre-net, fused in the library), bf16"}
 
 
 def _max_over_ranks(x, dev, world):
