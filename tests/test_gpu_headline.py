@@ -361,3 +361,33 @@ def test_layer_chain_kernel_equals_per_layer_launches(P16, monkeypatch, N, cfg, 
         out = h.sample(z, x0, nz, **kw)
         assert torch.equal(out, ref), (rep, float((out - ref).abs().max()))
     assert h.launch_count() / 4 < 0.5 * l_ref  # 4 kernels per step and chunk instead of 22
+
+
+def test_sample_tokens_glue_matches_the_reference_gather_scatter():
+    """patch.sample_masked_tokens (MAR:1086-1116 around diffloss.sample): with every token masked (num_iter = 1, all
+    shipped configs) the sync-free form gives exactly what the reference's nonzero-gather / sample / nonzero-scatter
+    sequence gives on the same RNG state; with a partial mask it follows the reference's sequence itself."""
+    dev = _cuda()
+    from unified_video_action_b200 import DiffLoss, sample_masked_tokens
+
+    P = O.make_params(16, 768, 1024, 6, seed=1)
+    head = DiffLoss(16, 768, 6, 1024, "20", n_frames=4, language_emb_model=None, language_emb_model_type=None)
+    head.net.load_state_dict({k: _T(v) for k, v in P.items()})
+    head = head.to(dev)
+    B, S = 2, 64
+    g = torch.Generator().manual_seed(6)
+    z = torch.randn(B, S, 768, generator=g).to(dev)
+    cur = torch.randn(B, S, 16, generator=g).to(dev)
+    for mask in (torch.ones(B, S, dtype=torch.bool), torch.rand(B, S, generator=g) > 0.5):
+        mask = mask.to(dev)
+        torch.manual_seed(77)
+        ref = cur.clone()
+        ref[mask.nonzero(as_tuple=True)] = head.sample(z[mask.nonzero(as_tuple=True)], 0.95, 1.0)   # MAR:1090, 1101, 1112
+        torch.manual_seed(77)
+        out = sample_masked_tokens(head, z, mask, cur, 0.95, 1.0)
+        assert torch.equal(out, ref)
+        assert torch.equal(out[~mask], cur[~mask])
+    torch.manual_seed(77)
+    full = sample_masked_tokens(head, z, torch.ones(B, S, dtype=torch.bool, device=dev), cur, 0.95, 1.0, all_masked=True)
+    torch.manual_seed(77)
+    assert torch.equal(full, head.sample(z.reshape(-1, 768), 0.95, 1.0).reshape(B, S, 16))

@@ -7,9 +7,9 @@ PyTorch; ``patch(mar_model)`` swaps the heads of a reference ``MAR`` in place.
 """
 from .diffusion_loss import DiffLoss, SimpleMLPAdaLN, param_names  # noqa: F401
 from .diffusion_action_loss import DiffActLoss  # noqa: F401
-from .patch import patch, shard_rows, allreduce_head_grads, overlap_allreduce  # noqa: F401
+from .patch import patch, shard_rows, allreduce_head_grads, overlap_allreduce, sample_masked_tokens  # noqa: F401
 from .optim import HeadAdamW, ema_decay_at  # noqa: F401
 from .checkpoint import export_head_state_dict, head_state_dicts, load_reference_checkpoint  # noqa: F401
 
-__all__ = ["DiffLoss", "DiffActLoss", "SimpleMLPAdaLN", "param_names", "patch", "shard_rows", "allreduce_head_grads", "overlap_allreduce", "HeadAdamW", "ema_decay_at",
+__all__ = ["DiffLoss", "DiffActLoss", "SimpleMLPAdaLN", "param_names", "patch", "shard_rows", "allreduce_head_grads", "overlap_allreduce", "sample_masked_tokens", "HeadAdamW", "ema_decay_at",
            "load_reference_checkpoint", "head_state_dicts", "export_head_state_dict"]

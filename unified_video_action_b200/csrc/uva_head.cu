@@ -27,7 +27,21 @@
 #include "optim.cuh"
 #include "prenet_kernels.cuh"
 
+#include <nvtx3/nvToolsExt.h>
+
 using namespace uva;
+
+// NVTX ranges around every compute entry point of the C ABI (tracing).  UVA_NVTX=1 turns them on (read
+// once); a range covers the host-side enqueue, and ncu / nsys can filter on it (--nvtx --nvtx-include "uva_head_sample/").
+struct NvtxRange {
+  bool on;
+  explicit NvtxRange(const char* name) {
+    static const bool enabled = [] { const char* e = getenv("UVA_NVTX"); return e && atoi(e) != 0; }();
+    on = enabled;
+    if (on) nvtxRangePushA(name);
+  }
+  ~NvtxRange() { if (on) nvtxRangePop(); }
+};
 
 // ----------------------------------------------------------------------------------------------
 // errors

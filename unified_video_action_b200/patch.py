@@ -65,6 +65,41 @@ def shard_rows(n_rows: int, rank: int, world_size: int, pair_halves: bool = Fals
     return begin, begin + base + (1 if rank < rem else 0)
 
 
+@torch.no_grad()
+def sample_masked_tokens(head: DiffLoss, z: torch.Tensor, mask_to_pred: torch.Tensor, cur_tokens: torch.Tensor,
+                         temperature: float = 1.0, cfg: float = 1.0, all_masked: Optional[bool] = None) -> torch.Tensor:
+    """The glue around ``diffloss.sample`` inside ``MAR.sample_tokens`` (mar_con_unified.py:1086-1116) without its
+    host round trips.  The reference gathers the rows to predict with ``z[mask_to_pred.nonzero(as_tuple=True)]``
+    (a device-to-host sync for the row count), samples them, and scatters the result back with a second
+    ``nonzero``.  Here: z [B, S, Z], mask_to_pred [B, S] (bool), cur_tokens [B, S, C] -> new tokens [B, S, C].
+
+    ``all_masked=True`` (what every shipped config does: ``num_iter = 1`` predicts all tokens in one pass, uva.yaml:42)
+    samples all B*S rows - the same rows in the same order as the reference's gather, hence the same RNG draws and
+    the same samples - and writes them with one ``torch.where``: no ``nonzero``, no sync.  ``all_masked=None`` checks
+    the mask (one sync, still one fewer than the reference) and falls back to the reference's gather / scatter for a
+    partial mask (``num_iter > 1``), so the RNG consumption stays the reference's in every case.  cfg != 1 follows the
+    reference's row layout (cond || uncond halves of z; only the cond half is scattered, MAR:1105-1116)."""
+    B, S = mask_to_pred.shape
+    C = cur_tokens.shape[-1]
+    if all_masked is None:
+        all_masked = bool(mask_to_pred.all())
+    flat = cur_tokens.reshape(B * S, C)
+    if all_masked:
+        rows = z.reshape(-1, z.shape[-1])
+        sampled = head.sample(rows, temperature, cfg)
+        if not cfg == 1.0:
+            sampled = sampled[: B * S]
+        return torch.where(mask_to_pred.reshape(B * S, 1), sampled.to(flat.dtype), flat).reshape(B, S, C)
+    m = mask_to_pred if cfg == 1.0 else torch.cat([mask_to_pred, mask_to_pred], dim=0)
+    rows = z[m.nonzero(as_tuple=True)]
+    sampled = head.sample(rows, temperature, cfg)
+    if not cfg == 1.0:
+        sampled, _ = sampled.chunk(2, dim=0)
+    out = flat.clone().reshape(B, S, C)
+    out[mask_to_pred.nonzero(as_tuple=True)] = sampled.to(out.dtype)
+    return out
+
+
 def _shared_flat(grads):
     """If every gradient is a contiguous view into one storage (what ``_FusedLoss.backward`` produces),
     return a 1-D tensor over the span they occupy; else None.  Gaps of the span hold alignment padding
