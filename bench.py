@@ -348,12 +348,12 @@ def train_extras(dev, world):
     """extras.C2_train at every N: the joint training step WITH the head-gradient all-reduce (the path's only
     collective), fp32 and bf16 on the wire, plus the collective alone with its bus bandwidth.
     Times are the max over ranks."""
-    res = measure_train(dev, world)
+    res = measure_train(dev, world, iters=20)
     res["ms_per_step"] = _max_over_ranks(res["ms_per_step"], dev, world)
     res["rows_per_s_per_gpu"] = res["rows_per_gpu"] / (res["ms_per_step"] / 1e3)
     res["tflops_per_gpu"] = (res["rows_per_gpu"] - 16 * 16) * TRAIN_FLOP_PER_ROW / (res["ms_per_step"] / 1e3) / 1e12
     if world > 1:
-        b = measure_train(dev, world, bf16_wire=True)
+        b = measure_train(dev, world, iters=20, bf16_wire=True)
         res["bf16_wire"] = {"ms_per_step": _max_over_ranks(b["ms_per_step"], dev, world), "p50_ms": b["p50_ms"]}
         ar = measure_allreduce(dev, world)
         for k in ar:
