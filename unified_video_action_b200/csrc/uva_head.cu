@@ -273,6 +273,7 @@ struct UvaHead {
   };
   std::vector<TrainGraph> tgraphs;
   bool train_graph = true;
+  int64_t train_graph_rows = 1024;  // UVA_TRAIN_GRAPH_ROWS: largest batch whose loss_fwd / loss_bwd replay from a CUDA graph
   bool timing = false;
   int cur_cat = 0;
   struct TimedLaunch { int cat; cudaEvent_t a, b; };
@@ -418,6 +419,7 @@ extern "C" int uva_head_create(const UvaHeadDesc* desc, UvaHead** out) {
   if (const char* e = getenv("UVA_PDL")) h->pdl = atoi(e) != 0;
   if (const char* e = getenv("UVA_FINAL_TC")) h->final_tc = atoi(e) != 0;
   if (const char* e = getenv("UVA_TRAIN_GRAPH")) h->train_graph = atoi(e) != 0;
+  if (const char* e = getenv("UVA_TRAIN_GRAPH_ROWS")) h->train_graph_rows = atol(e);
   if (const char* e = getenv("UVA_FUSE_COLSUM")) h->fuse_colsum = atoi(e) != 0;
   if (const char* e = getenv("UVA_EPI_COLSUM")) h->epi_colsum = atoi(e) != 0;
   if (const char* e = getenv("UVA_PDL_BIG")) h->pdl_big = atoi(e) != 0;
