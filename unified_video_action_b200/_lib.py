@@ -416,8 +416,9 @@ class Head:
             raise RuntimeError(f"pre-net: z must be [B, {T * 256}, {self.Z}], got {tuple(z.shape)}")
         out = torch.empty(B, J, self.Z, dtype=torch.float32, device=z.device)
         ws = self.prenet_workspace(B, True) if train else self.prenet_workspace(B, False)
-        if train:
-            self.prenet_gen = getattr(self, "prenet_gen", 0) + 1
+        # every forward rewrites the buffers a pending backward would read (an inference call shares them): the
+        # generation counter lets that backward notice and redo its forward
+        self.prenet_gen = getattr(self, "prenet_gen", 0) + 1
         _check(lib().uva_head_prenet_forward(self._h, z.data_ptr(), B, out.data_ptr(), ws.data_ptr(), ws.numel(), int(train),
                                              _stream()), "uva_head_prenet_forward")
         return out
