@@ -98,6 +98,20 @@ size_t uva_head_workspace_bytes(const UvaHead* h, int64_t rows, int32_t what);
 int uva_head_net_forward(UvaHead* h, const float* x, const int64_t* t, const float* c, int64_t N,
                          float* out, void* ws, size_t ws_bytes, void* stream);
 
+/* The same computation for a small batch with NO workspace argument and NO allocation of any kind (no cudaMalloc,
+ * cudaFree or allocating library call).  This entry point has no counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  Its scratch is one file-scope `static __device__` array of 16 MiB that
+ * every GPU loading the library holds until exit; the buffers of round_up(N, 128) rows must fit in it:
+ * N <= uva_head_static_max_rows(h) = 256 rows in bf16 mode / 128 rows in fp32 mode at the reference geometry
+ * (W = 1024, depth = 6, Z = 768).  A larger N returns UVA_ERR_INVALID with a message that names the limit.
+ * Every call shares the array, which keeps the previous call's contents (the entry point clears what it needs):
+ * calls that overlap on the GPU - two streams, two threads, two handles - RACE on it; serialise them on one stream.
+ * Same inputs, outputs and results as uva_head_net_forward. */
+int uva_head_net_forward_static(UvaHead* h, const float* x, const int64_t* t, const float* c, int64_t N,
+                                float* out, void* stream);
+int64_t uva_head_static_max_rows(const UvaHead* h);
+
 /* DiffLoss.sample / DiffActLoss.sample after the pre-net (DL:68-90, DAL:207-227) =
  * p_sample_loop (GD:446-541) over p_sample (GD:395-444) / p_mean_variance (GD:260-346) with the
  * wrapped model (RS:115-127) and optionally forward_with_cfg (DL:285-293).

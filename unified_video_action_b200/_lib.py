@@ -98,6 +98,7 @@ _lock = threading.Lock()
 SYMBOLS = [
     "uva_head_num_params", "uva_head_param_numel", "uva_head_create", "uva_head_destroy",
     "uva_schedule_table", "uva_head_load_weights", "uva_head_workspace_bytes", "uva_head_net_forward",
+    "uva_head_net_forward_static", "uva_head_static_max_rows",
     "uva_head_prenet_num_params", "uva_head_prenet_load_weights", "uva_head_prenet_workspace_bytes",
     "uva_head_prenet_forward", "uva_head_prenet_backward",
     "uva_head_sample", "uva_head_sample_from_decoder", "uva_decoder_tail_rows", "uva_head_loss_fwd", "uva_head_loss_bwd", "uva_head_launch_count",
@@ -132,6 +133,10 @@ def lib() -> ctypes.CDLL:
         L.uva_head_workspace_bytes.argtypes = [vp, i64, i32]
         L.uva_head_net_forward.restype = ctypes.c_int
         L.uva_head_net_forward.argtypes = [vp, vp, vp, vp, i64, vp, vp, ctypes.c_size_t, vp]
+        L.uva_head_net_forward_static.restype = ctypes.c_int
+        L.uva_head_net_forward_static.argtypes = [vp, vp, vp, vp, i64, vp, vp]
+        L.uva_head_static_max_rows.restype = ctypes.c_int64
+        L.uva_head_static_max_rows.argtypes = [vp]
         L.uva_head_sample.restype = ctypes.c_int
         L.uva_head_sample.argtypes = [vp, vp, vp, vp, vp, vp, f32, f32, i32, i32, i32, i64, vp, vp, ctypes.c_size_t, vp]
         L.uva_head_sample_from_decoder.restype = ctypes.c_int
@@ -319,6 +324,20 @@ class Head:
         ws = self.workspace(N, 0)
         _check(lib().uva_head_net_forward(self._h, x.data_ptr(), t.data_ptr(), c.data_ptr(), N, out.data_ptr(),
                                           ws.data_ptr(), ws.numel(), _stream()), "uva_head_net_forward")
+        return out
+
+    def static_max_rows(self) -> int:
+        return int(lib().uva_head_static_max_rows(self._h))
+
+    def net_forward_static(self, x: torch.Tensor, t: torch.Tensor, c: torch.Tensor, out: torch.Tensor) -> torch.Tensor:
+        """``net_forward`` on the library's static device scratch (``uva_head_net_forward_static``): no workspace and no
+        allocation inside the call - inputs must already be fp32 / int64, contiguous and on the device, ``out`` is the
+        caller's ``[N, 2C]`` fp32 buffer.  At most ``static_max_rows()`` rows; concurrent calls race on the scratch."""
+        for name, v, dt in (("x", x, torch.float32), ("c", c, torch.float32), ("t", t, torch.int64), ("out", out, torch.float32)):
+            if v.dtype != dt or not v.is_contiguous() or not v.is_cuda:
+                raise RuntimeError(f"net_forward_static: {name} must be a contiguous CUDA {dt} tensor")
+        _check(lib().uva_head_net_forward_static(self._h, x.data_ptr(), t.data_ptr(), c.data_ptr(), x.shape[0],
+                                                 out.data_ptr(), _stream()), "uva_head_net_forward_static")
         return out
 
     def sample(self, z, x_init, step_noise, temperature=1.0, cfg=1.0, clip_denoised=False, teacher=None,

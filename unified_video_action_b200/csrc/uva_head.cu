@@ -9,6 +9,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -591,3 +592,79 @@ extern "C" int uva_adamw_ema_step(int32_t n_tensors, float* const* params, const
 #include "collective.inc"
 #include "head_train.inc"
 #include "head_prenet.inc"
+
+// ----------------------------------------------------------------------------------------------
+// uva_head_net_forward_static: SimpleMLPAdaLN.forward for a small batch WITHOUT a caller workspace and without any
+// allocation.  No counterpart in the reference: added for callers that cannot
+// call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+//
+// The scratch (the InferWs buffers of head_infer.inc: cemb, ys, mod, h, a, u, net output, bf16 operand rows, LayerNorm
+// statistics) lives in ONE file-scope device array of kStaticScratchBytes = 16 MiB, which every GPU that loads the
+// library holds until the process exits.  That bounds the batch: the buffers of round_up(N, 128) rows must fit, i.e.
+// N <= 256 rows in bf16 mode and N <= 128 rows in fp32 mode at the reference geometry (W = 1024, depth = 6, Z = 768).
+//
+// In host code `g_static_scratch` is a host-side stand-in, not a device address: the device address is taken once per
+// device, with that device current, through cudaGetSymbolAddress, and only that pointer is handed to the kernels.
+// Every call (of every handle, on every stream) shares the array and it keeps the last call's contents: nothing in it
+// has to start at zero for the kernels of this path (each buffer is written before it is read), the LayerNorm
+// statistics and the completion counters are cleared anyway; two calls that overlap on the GPU (two streams, two
+// threads, two handles) RACE on it - serialise them on one stream.
+// ----------------------------------------------------------------------------------------------
+static constexpr size_t kStaticScratchBytes = (size_t)16 << 20;
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
+
+static constexpr int kStaticMaxDevices = 64;
+static void* g_static_ptr[kStaticMaxDevices] = {};  // device address of g_static_scratch, per device ordinal
+static std::mutex g_static_mu;
+
+// device address of the scratch array on the current device (looked up once per device)
+static int static_scratch_ptr(void** out) {
+  int dev = -1;
+  CUDA_TRY(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kStaticMaxDevices) return fail(UVA_ERR_INVALID, "net_forward_static: device ordinal %d not supported", dev);
+  std::lock_guard<std::mutex> lk(g_static_mu);
+  if (!g_static_ptr[dev]) {
+    void* p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress((void**)&p, g_static_scratch);
+    if (e != cudaSuccess || !p)
+      return fail(UVA_ERR_CUDA, "net_forward_static: cudaGetSymbolAddress failed on device %d: %s", dev, cudaGetErrorString(e));
+    g_static_ptr[dev] = p;
+  }
+  *out = g_static_ptr[dev];
+  return UVA_OK;
+}
+
+extern "C" int64_t uva_head_static_max_rows(const UvaHead* h) {
+  if (!h) return 0;
+  int64_t best = 0;
+  for (int64_t R = UG_BM; R <= 4096; R += UG_BM) {
+    if (carve_infer(h, nullptr, R).bytes > kStaticScratchBytes) break;
+    best = R;
+  }
+  return best;
+}
+
+extern "C" int uva_head_net_forward_static(UvaHead* h, const float* x, const int64_t* t, const float* c, int64_t N,
+                                           float* out, void* stream) {
+  NvtxRange nvtx_("uva_head_net_forward_static");
+  if (!h || !x || !t || !c || !out) return fail(UVA_ERR_INVALID, "net_forward_static: null argument");
+  if (!h->weights_loaded) return fail(UVA_ERR_STATE, "net_forward_static: weights not loaded");
+  if (N <= 0) return UVA_OK;
+  const UvaHeadDesc& d = h->d;
+  const int64_t R = (N + UG_BM - 1) / UG_BM * UG_BM;
+  const size_t need = carve_infer(h, nullptr, R).bytes;
+  if (need > kStaticScratchBytes)
+    return fail(UVA_ERR_INVALID, "net_forward_static: N = %lld rows need %zu bytes of scratch, the static array holds %zu (at most %lld rows for this head; use uva_head_net_forward with a workspace)",
+                (long long)N, need, kStaticScratchBytes, (long long)uva_head_static_max_rows(h));
+  void* base = nullptr;
+  UVA_TRY(static_scratch_ptr(&base));
+  InferWs w = carve_infer(h, base, R);
+  cudaStream_t st = (cudaStream_t)stream;
+  // shared with every earlier call: the small accumulator-like regions start from zero
+  CUDA_TRY(cudaMemsetAsync(w.stats, 0, (size_t)((uint8_t*)base + w.bytes - (uint8_t*)w.stats), st));
+  UVA_TRY(compute_cemb(h, w, c, 0, 0, N, st));
+  UVA_TRY(run_stack_mode(h, w, N, x, 0, t, 0, st));
+  CUDA_TRY(cudaMemcpy2DAsync(out, (size_t)2 * d.C * 4, w.netout, (size_t)kNetLd * 4, (size_t)2 * d.C * 4, (size_t)N,
+                             cudaMemcpyDeviceToDevice, st));
+  return UVA_OK;
+}
