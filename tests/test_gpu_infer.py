@@ -657,3 +657,28 @@ def test_lnmod_prephase_equals_separate_launch(video, monkeypatch, N, k_end):
         outs[flag] = a
     assert torch.equal(outs["0"], outs["1"])
     assert counts["1"] <= counts["0"] - 5 * k_end, counts
+
+
+@pytest.mark.parametrize("N,cfg", [(896, 1.0), (512, 3.0), (300, 1.0), (64, 1.0), (1024, 1.0)])
+def test_hoist_overlap_equals_serial_hoist(video, monkeypatch, N, cfg):
+    """Graph path (33 .. 1024 rows): the modulation table of the NEXT half group of denoise steps is computed on the
+    handle's hoist stream, on the SMs the chain's one-wave GEMMs leave free, while the chain of the current half group
+    runs (head_small.inc).  Same kernels on the same operands -> bit-identical to the serial hoist, eager call, graph
+    capture and graph replay alike (three calls: a stale table half would show up on the later ones)."""
+    dev, g, P = video
+    gen = torch.Generator().manual_seed(N)
+    z = torch.randn(N, 768, generator=gen).to(dev)
+    x0 = torch.randn(N, 16, generator=gen).to(dev)
+    if cfg != 1.0:
+        x0[N // 2:] = x0[:N // 2]
+    nz = torch.randn(100, N, 16, generator=gen).to(dev)
+    outs = {}
+    for flag in ("0", "1"):
+        monkeypatch.setenv("UVA_HOIST_OVERLAP", flag)
+        h = _head(16, 768, 1024, 6, P, 1, dev)
+        calls = [h.sample(z, x0, nz, temperature=0.95, cfg=cfg).clone() for _ in range(3)]
+        torch.cuda.synchronize()
+        assert torch.equal(calls[0], calls[1]) and torch.equal(calls[0], calls[2]), flag
+        assert torch.isfinite(calls[0]).all()
+        outs[flag] = calls[0]
+    assert torch.equal(outs["0"], outs["1"])

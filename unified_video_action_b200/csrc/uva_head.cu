@@ -259,6 +259,14 @@ struct UvaHead {
   bool use_chain = true;         // UVA_CHAIN: persistent chain kernel (chain_kernel.cuh)
   int64_t chain_rows = 32;       // UVA_CHAIN_ROWS: largest batch it takes (its time grows with rows / 16)
   bool use_graph = true;         // UVA_GRAPH
+  // UVA_HOIST_OVERLAP: graph path (33 .. small_rows rows): the modulation table is hoisted in half groups and the GEMM of
+  // the NEXT half group runs on its own stream, on hoist_sms SMs (UVA_HOIST_SMS; 0 = sized from the row count), beside the
+  // launch-bound chain of the current one, whose tiles are then picked for the remaining chain_sms SMs
+  bool hoist_overlap = true;
+  int hoist_sms = 0;
+  int chain_sms = 0;             // SMs the chain's one-wave tile choice may fill right now (0: all)
+  cudaStream_t hoist_st = nullptr;
+  cudaEvent_t ev_hfork = nullptr, ev_hdone = nullptr;
   bool bn32 = true;              // UVA_BN32: 128 x 32 tiles for the W x W GEMMs when rows <= 128 (32 CTAs stream the weight)
   struct SmallGraph {
     const void* ws; int64_t N; int k_begin, k_end, clip; float temperature, cfg;
@@ -418,6 +426,8 @@ extern "C" int uva_head_create(const UvaHeadDesc* desc, UvaHead** out) {
   if (const char* e = getenv("UVA_FUSE_DDPM")) h->fuse_ddpm = atoi(e) != 0;
   if (const char* e = getenv("UVA_FUSE_INPROJ")) h->fuse_inproj = atoi(e) != 0;
   if (const char* e = getenv("UVA_PDL")) h->pdl = atoi(e) != 0;
+  if (const char* e = getenv("UVA_HOIST_OVERLAP")) h->hoist_overlap = atoi(e) != 0;
+  if (const char* e = getenv("UVA_HOIST_SMS")) h->hoist_sms = atoi(e);
   if (const char* e = getenv("UVA_FINAL_TC")) h->final_tc = atoi(e) != 0;
   if (const char* e = getenv("UVA_TRAIN_GRAPH")) h->train_graph = atoi(e) != 0;
   if (const char* e = getenv("UVA_TRAIN_GRAPH_ROWS")) h->train_graph_rows = atol(e);
@@ -430,6 +440,9 @@ extern "C" int uva_head_create(const UvaHeadDesc* desc, UvaHead** out) {
   CUDA_TRY(cudaStreamCreateWithFlags(&h->side, cudaStreamNonBlocking));
   CUDA_TRY(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
   CUDA_TRY(cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming));
+  CUDA_TRY(cudaStreamCreateWithFlags(&h->hoist_st, cudaStreamNonBlocking));
+  CUDA_TRY(cudaEventCreateWithFlags(&h->ev_hfork, cudaEventDisableTiming));
+  CUDA_TRY(cudaEventCreateWithFlags(&h->ev_hdone, cudaEventDisableTiming));
   h->gen = create_schedule(d.T_train, d.T_gen);
   h->train = create_schedule(d.T_train, d.T_train);
   int rc = upload_tables(h->train, h->dtrain, &h->d_tables);
@@ -537,6 +550,9 @@ extern "C" void uva_head_destroy(UvaHead* h) {
   if (h->side) cudaStreamDestroy(h->side);
   if (h->ev_fork) cudaEventDestroy(h->ev_fork);
   if (h->ev_join) cudaEventDestroy(h->ev_join);
+  if (h->hoist_st) cudaStreamDestroy(h->hoist_st);
+  if (h->ev_hfork) cudaEventDestroy(h->ev_hfork);
+  if (h->ev_hdone) cudaEventDestroy(h->ev_hdone);
   delete h;
 }
 
