@@ -57,6 +57,9 @@ __global__ void k_final_dgrad(const float* __restrict__ dnet, int ldn, const flo
 }
 
 constexpr int FW_ROWS = 128;  // rows per block of the skinny weight-gradient kernels
+constexpr int IW_ROWS = 256;  // most rows a block of k_inproj_wgrad takes (its x_t rows are staged in shared memory)
+constexpr int IW_STAGES = 3;
+constexpr int kIwRingBytes = IW_STAGES * 4 * 256 * 16;
 template <typename TA>
 __global__ void __launch_bounds__(256)
 k_final_wgrad(const float* __restrict__ dnet, int ldn, const TA* __restrict__ a, float* __restrict__ dWl,
@@ -103,51 +106,109 @@ k_final_wgrad(const float* __restrict__ dnet, int ldn, const TA* __restrict__ a,
   }
 }
 
+// rows per block of k_inproj_wgrad: one wave of ~2 blocks per SM over the 4 x gridDim.y grid, a multiple of 16, <= IW_ROWS
+inline int iw_rows_per_block(int64_t rows, int W, int num_sms) {
+  const int gx = (W + 255) / 256;
+  int64_t gy = (2 * num_sms + gx - 1) / gx;
+  int64_t rpb = (rows + gy - 1) / gy;
+  rpb = (rpb + 15) / 16 * 16;
+  if (rpb < 16) rpb = 16;
+  if (rpb > IW_ROWS) rpb = IW_ROWS;
+  return (int)rpb;
+}
+
 // ------------------------------------------------------------------------------------------
 // input_proj backward (DL:268): h0 = x_t . Wi^T + bi with K = C <= 16:
 //   dWi[j, c] += sum_r dh[r, j] x_t[r, c],  dbi[j] += sum_r dh[r, j].
 // ------------------------------------------------------------------------------------------
+// A block takes 256 columns (64 threads x 4 adjacent columns, 16-byte loads) x rows_per_block rows (4 row lanes of 64
+// threads; iw_rows_per_block() sizes the grid for one wave of two blocks per SM); the 4 lanes are combined in shared memory and the block adds its [256, C] patch with coalesced
+// reductions (the patch is contiguous in dWi).  W % 4 == 0.
 __global__ void __launch_bounds__(256)
 k_inproj_wgrad(const float* __restrict__ dh, const float* __restrict__ xt, float* __restrict__ dWi,
-               float* __restrict__ dbi, int64_t rows, int W, int C) {
-  const int j = blockIdx.x * blockDim.x + threadIdx.x;
-  const int64_t r0 = (int64_t)blockIdx.y * FW_ROWS;
-  const int64_t r1 = (r0 + FW_ROWS < rows) ? r0 + FW_ROWS : rows;
-  if (j >= W) return;
-  float acc[16];
+               float* __restrict__ dbi, int64_t rows, int W, int C, int rows_per_block) {
+  __shared__ float patch[256 * 17];  // [column][16 c + bias], combined over the row lanes
+  __shared__ __align__(16) float xs[IW_ROWS * 16];  // the block's x_t rows, zero padded to 16 channels
+  extern __shared__ float4 ring[];  // [IW_STAGES][4][256]: kIwRingBytes of dynamic shared memory
+  const int tx = threadIdx.x & 63, ty = threadIdx.x >> 6;
+  const int j = blockIdx.x * 256 + tx * 4;
+  const int64_t r0 = (int64_t)blockIdx.y * rows_per_block;  // rows_per_block <= IW_ROWS
+  const int64_t r1 = (r0 + rows_per_block < rows) ? r0 + rows_per_block : rows;
+  for (int e = threadIdx.x; e < rows_per_block * 16; e += 256) {
+    const int rr = e >> 4, c = e & 15;
+    xs[e] = (r0 + rr < r1 && c < C) ? xt[(r0 + rr) * C + c] : 0.f;
+  }
+  __syncthreads();
+  float acc[4][16];
+  float sb[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-  for (int c = 0; c < 16; ++c) acc[c] = 0.f;
-  float sb = 0.f;
-  if (C == 16) {
-#pragma unroll 2
-    for (int64_t r = r0; r < r1; ++r) {
-      const float d = dh[r * W + j];
-      sb += d;
-      const float4* xp = reinterpret_cast<const float4*>(xt + r * 16);
+  for (int k = 0; k < 4; ++k)
 #pragma unroll
-      for (int c4 = 0; c4 < 4; ++c4) {
-        const float4 x = __ldg(xp + c4);
-        acc[4 * c4] = fmaf(d, x.x, acc[4 * c4]);
-        acc[4 * c4 + 1] = fmaf(d, x.y, acc[4 * c4 + 1]);
-        acc[4 * c4 + 2] = fmaf(d, x.z, acc[4 * c4 + 2]);
-        acc[4 * c4 + 3] = fmaf(d, x.w, acc[4 * c4 + 3]);
+    for (int c = 0; c < 16; ++c) acc[k][c] = 0.f;
+  if (j < W) {
+    // d h streams through a ring of IW_STAGES thread-private stages (4 rows x 16 bytes per thread and stage, cp.async):
+    // the loads of the next two stages are in flight while one is consumed, without holding registers for them
+    const int n_it = (int)((r1 - r0 + 15) / 16);
+    auto issue = [&](int it) {
+      if (it < n_it) {
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int64_t ru = r0 + ty + 16 * it + 4 * u;
+          const bool on = ru < r1;
+          const float* src = dh + (on ? ru : r0) * W + j;
+          const uint32_t dst = smem_u32(&ring[((it % IW_STAGES) * 4 + u) * 256 + threadIdx.x]);
+          asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(on ? 16 : 0) : "memory");
+        }
+      }
+      asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    for (int it = 0; it < IW_STAGES - 1; ++it) issue(it);
+    for (int it = 0; it < n_it; ++it) {
+      issue(it + IW_STAGES - 1);
+      asm volatile("cp.async.wait_group %0;" ::"n"(IW_STAGES - 1) : "memory");
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const float4 d = ring[((it % IW_STAGES) * 4 + u) * 256 + threadIdx.x];
+        const int rr = ty + 16 * it + 4 * u;  // (rows past the end were zero-filled)
+        const float4* xp = reinterpret_cast<const float4*>(xs + (rr < IW_ROWS ? rr : 0) * 16);
+        const float dv[4] = {d.x, d.y, d.z, d.w};
+#pragma unroll
+        for (int c4 = 0; c4 < 4; ++c4) {
+          const float4 x = xp[c4];
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            acc[k][4 * c4] = fmaf(dv[k], x.x, acc[k][4 * c4]);
+            acc[k][4 * c4 + 1] = fmaf(dv[k], x.y, acc[k][4 * c4 + 1]);
+            acc[k][4 * c4 + 2] = fmaf(dv[k], x.z, acc[k][4 * c4 + 2]);
+            acc[k][4 * c4 + 3] = fmaf(dv[k], x.w, acc[k][4 * c4 + 3]);
+          }
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) sb[k] += dv[k];
       }
     }
-  } else {
-    for (int64_t r = r0; r < r1; ++r) {
-      const float d = dh[r * W + j];
-      sb += d;
+  }
+  // combine the 4 row lanes: lane 0 stores, the others add in turn
+  for (int turn = 0; turn < 4; ++turn) {
+    if (ty == turn) {
 #pragma unroll
-      for (int c = 0; c < 16; ++c)
-        if (c < C) acc[c] = fmaf(d, xt[r * C + c], acc[c]);
+      for (int k = 0; k < 4; ++k) {
+        float* pr = patch + (tx * 4 + k) * 17;
+#pragma unroll
+        for (int c = 0; c < 16; ++c) pr[c] = (turn ? pr[c] : 0.f) + acc[k][c];
+        pr[16] = (turn ? pr[16] : 0.f) + sb[k];
+      }
+    }
+    __syncthreads();
+  }
+  const int j0 = blockIdx.x * 256;
+  if (dWi) {
+    for (int e = threadIdx.x; e < 256 * C; e += 256) {
+      const int col = e / C, c = e - col * C;
+      if (j0 + col < W) atomicAdd(dWi + (int64_t)j0 * C + e, patch[col * 17 + c]);
     }
   }
-  if (dWi) {
-#pragma unroll
-    for (int c = 0; c < 16; ++c)
-      if (c < C) atomicAdd(dWi + (int64_t)j * C + c, acc[c]);
-  }
-  if (dbi) atomicAdd(dbi + j, sb);
+  if (dbi && j0 + (int)threadIdx.x < W) atomicAdd(dbi + j0 + threadIdx.x, patch[threadIdx.x * 17 + 16]);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -158,14 +219,71 @@ k_inproj_wgrad(const float* __restrict__ dh, const float* __restrict__ xt, float
 // four columns): the bias gradients  db2 += sum_r dq,  d(adaLN bias, gate part) += sum_r dgate  accumulated in
 // registers over the thread's rows and added with one atomic per column and thread — the two separate
 // column-sum passes over dq and dgate disappear.
+// The block is (blockDim.x / (W / 4)) row lanes of W / 4 threads: the lanes are combined in shared memory before the
+// atomics, so that an address sees one reduction per BLOCK - the end-of-kernel atomics of 592 blocks x 2 W columns on
+// 64 L2 sectors cost 20 us of a 57 us kernel (measured, scripts/rowkernel_bench.cu); 148 blocks of 4 lanes: 5 us.
 template <typename TA>
-__global__ void k_gate_bwd(const float* __restrict__ dh, const TA* __restrict__ gate, const TA* __restrict__ q,
-                           int64_t ldmod, TA* __restrict__ dq, TA* __restrict__ dgate, int64_t rows, int W,
-                           float* __restrict__ sum_dq = nullptr, float* __restrict__ sum_dgate = nullptr) {
+__global__ void __launch_bounds__(1024)
+k_gate_bwd(const float* __restrict__ dh, const TA* __restrict__ gate, const TA* __restrict__ q,
+           int64_t ldmod, TA* __restrict__ dq, TA* __restrict__ dgate, int64_t rows, int W,
+           float* __restrict__ sum_dq = nullptr, float* __restrict__ sum_dgate = nullptr) {
   const int wq = W / 4;
   const int64_t n = rows * wq;
   float s1[4] = {0.f, 0.f, 0.f, 0.f}, s2[4] = {0.f, 0.f, 0.f, 0.f};
   int jcol = -1;
+  if ((int)blockDim.x % wq == 0) {
+    // row-lane form: every thread keeps its 4 columns; 2 rows per iteration with all 6 loads requested before the first
+    // use (the kernel is bound by bytes in flight per SM, not by arithmetic)
+    __shared__ float comb[2 * 1024];  // (W <= 1024 in this form: blockDim.x <= 1024)
+    constexpr int U = 2;
+    const int lanes = (int)blockDim.x / wq;
+    const int tx = (int)threadIdx.x % wq, ty = (int)threadIdx.x / wq;
+    const int j = tx * 4;
+    const int64_t step = (int64_t)gridDim.x * lanes;
+    for (int64_t r = (int64_t)blockIdx.x * lanes + ty; r < rows; r += U * step) {
+      float4 d[U];
+      float g[U][4], qq[U][4];
+      bool on[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int64_t ru = r + u * step;
+        on[u] = ru < rows;
+        if (on[u]) {
+          d[u] = *reinterpret_cast<const float4*>(dh + ru * W + j);
+          load4<TA>(gate + ru * ldmod + j, g[u]);
+          load4<TA>(q + ru * W + j, qq[u]);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        if (on[u]) {
+          const int64_t ru = r + u * step;
+          const float o1[4] = {d[u].x * g[u][0], d[u].y * g[u][1], d[u].z * g[u][2], d[u].w * g[u][3]};
+          const float o2[4] = {d[u].x * qq[u][0], d[u].y * qq[u][1], d[u].z * qq[u][2], d[u].w * qq[u][3]};
+          store4(dq + ru * W + j, o1);
+          store4(dgate + ru * ldmod + j, o2);
+#pragma unroll
+          for (int k = 0; k < 4; ++k) { s1[k] += o1[k]; s2[k] += o2[k]; }
+        }
+      }
+    }
+    if (sum_dq == nullptr && sum_dgate == nullptr) return;  // uniform
+    for (int turn = 0; turn < lanes; ++turn) {
+      if (ty == turn) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          comb[j + k] = (turn ? comb[j + k] : 0.f) + s1[k];
+          comb[W + j + k] = (turn ? comb[W + j + k] : 0.f) + s2[k];
+        }
+      }
+      __syncthreads();
+    }
+    for (int c = threadIdx.x; c < 2 * W; c += blockDim.x) {
+      float* dst = (c < W) ? sum_dq : sum_dgate;
+      if (dst) atomicAdd(dst + (c < W ? c : c - W), comb[c]);
+    }
+    return;
+  }
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     const int64_t r = i / wq;
     const int j = (int)(i - r * wq) * 4;
@@ -178,16 +296,8 @@ __global__ void k_gate_bwd(const float* __restrict__ dh, const TA* __restrict__ 
     const float o2[4] = {d.x * qq[0], d.y * qq[1], d.z * qq[2], d.w * qq[3]};
     store4(dq + r * W + j, o1);
     store4(dgate + r * ldmod + j, o2);
-#pragma unroll
-    for (int k = 0; k < 4; ++k) { s1[k] += o1[k]; s2[k] += o2[k]; }
   }
-  if (jcol >= 0) {
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      if (sum_dq) atomicAdd(sum_dq + jcol + k, s1[k]);
-      if (sum_dgate) atomicAdd(sum_dgate + jcol + k, s2[k]);
-    }
-  }
+  (void)jcol; (void)s1; (void)s2;  // (the generic form has no fixed columns per thread: the caller sums separately)
 }
 
 // ------------------------------------------------------------------------------------------
@@ -202,11 +312,21 @@ __global__ void __launch_bounds__(256)
 k_lnmod_bwd(const TA* __restrict__ da, const float* __restrict__ h, const float* __restrict__ stats,
             const float* __restrict__ ln_w, const float* __restrict__ ln_b, const TA* __restrict__ scale,
             int64_t ldmod, TA* __restrict__ dshift, TA* __restrict__ dscale, float* __restrict__ dh, int first,
-            float* __restrict__ dln_w, float* __restrict__ dln_b, int64_t rows) {
+            float* __restrict__ dln_w, float* __restrict__ dln_b, int64_t rows, float* __restrict__ dsum = nullptr) {
   constexpr int W = NV * 128;
   __shared__ float red[8][W / 4 + 1];  // reused for the two column sums (quarter of the row at a time)
+  // dsum ([2 W]: bias gradient of the shift | scale parts of this modulation = column sums of dshift | dscale; may be
+  // null): accumulated per warp in its own shared-memory rows (16-byte load + 4 adds + 16-byte store per 4 columns, no
+  // atomics: shared fp32 atomics are CAS loops), combined over the 8 warps at the end.  Needs 8 x 2 x W floats of
+  // dynamic shared memory.  Replaces a k_colsum pass over [rows, 2 W] per modulation.
+  extern __shared__ float4 wsum[];  // [8 warps][2][W / 4]
   const int lane = threadIdx.x & 31;
   const int wib = threadIdx.x >> 5;
+  float4* my_sum = wsum + (size_t)wib * 2 * (W / 4);
+  if (dsum) {
+#pragma unroll
+    for (int i = 0; i < 2 * NV; ++i) my_sum[lane + 32 * i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
   const int64_t warp_global = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int64_t warps_total = ((int64_t)gridDim.x * blockDim.x) >> 5;
   float aw[NV][4], ab[NV][4];
@@ -256,6 +376,13 @@ k_lnmod_bwd(const TA* __restrict__ da, const float* __restrict__ h, const float*
       }
       store4(dshift + r * ldmod + j, d);
       store4(dscale + r * ldmod + j, dsc);
+      if (dsum) {
+        float4 a0 = my_sum[lane + 32 * i], a1 = my_sum[W / 4 + lane + 32 * i];
+        a0.x += d[0]; a0.y += d[1]; a0.z += d[2]; a0.w += d[3];
+        a1.x += dsc[0]; a1.y += dsc[1]; a1.z += dsc[2]; a1.w += dsc[3];
+        my_sum[lane + 32 * i] = a0;
+        my_sum[W / 4 + lane + 32 * i] = a1;
+      }
     }
     s1 = warp_sum(s1) * (1.0f / W);
     s2 = warp_sum(s2) * (1.0f / W);
@@ -270,6 +397,16 @@ k_lnmod_bwd(const TA* __restrict__ da, const float* __restrict__ h, const float*
         o[0] += p.x; o[1] += p.y; o[2] += p.z; o[3] += p.w;
       }
       store4(dh + r * W + j, o);
+    }
+  }
+  if (dsum) {  // (uniform over the grid)
+    __syncthreads();
+    const float* all = reinterpret_cast<const float*>(wsum);
+    for (int c = threadIdx.x; c < 2 * W; c += blockDim.x) {
+      float t = 0.f;
+#pragma unroll
+      for (int w8 = 0; w8 < 8; ++w8) t += all[(size_t)w8 * 2 * W + c];
+      atomicAdd(dsum + c, t);
     }
   }
   if (dln_w == nullptr) return;  // uniform over the grid
