@@ -87,29 +87,35 @@ int main(int argc, char** argv) {
   time_it("k_gate_bwd no sums, 148 x 1024", RW * 12, 20, [&](int i) {
     k_gate_bwd<bf16><<<sms, 1024>>>(dh[i % SETS], mod + 2 * W, q[i % SETS], ldm, dq[i % SETS], dmod + 2 * W, N, W, nullptr, nullptr);
   });
-  time_it("k_lnmod_bwd grid 148, no column sums at all", RW * 20, 20, [&](int i) {
-    k_lnmod_bwd<bf16, 8><<<sms, 256>>>(da[i % SETS], h[i % SETS], stats, nullptr, nullptr, mod + W, ldm, dmod, dmod + W, dh[i % SETS], 0, nullptr, nullptr, N, nullptr);
-  });
-  time_it("k_lnmod_bwd grid 148, first (no dh read)", RW * 16, 20, [&](int i) {
-    k_lnmod_bwd<bf16, 8><<<sms, 256>>>(da[i % SETS], h[i % SETS], stats, nullptr, nullptr, mod + W, ldm, dmod, dmod + W, dh[i % SETS], 1, nullptr, nullptr, N, nullptr);
-  });
   // plain copy of the same byte count as a yardstick (read 8 B + write 4 B per element like k_gate_bwd)
   time_it("copy yardstick (float4 in, float2 out x 2 streams)", RW * 12, 20, [&](int i) {
     cudaMemcpyAsync(dh[(i + 1) % SETS], dh[i % SETS], N * W * 4, cudaMemcpyDeviceToDevice, 0);
     cudaMemcpyAsync(dq[(i + 1) % SETS], dq[i % SETS], N * W * 2, cudaMemcpyDeviceToDevice, 0);
   });
   // ---- LayerNorm-modulate backward
-  CK(cudaFuncSetAttribute(k_lnmod_bwd<bf16, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * 2 * 1024 * 4));
-  for (int blocks : {sms, 2 * sms, 4 * sms}) {
-    for (int with_sum = 0; with_sum < 2; ++with_sum) {
-      char nm[64];
-      snprintf(nm, sizeof nm, "k_lnmod_bwd grid %d%s", blocks, with_sum ? " + bias sums" : "");
-      time_it(nm, RW * 20, 20, [&](int i) {
-        k_lnmod_bwd<bf16, 8><<<blocks, 256, with_sum ? 8 * 2 * 1024 * 4 : 0>>>(da[i % SETS], h[i % SETS], stats, lnw, lnb, mod + W, ldm, dmod,
-                                                                               dmod + W, dh[i % SETS], 0, dlnw, dlnb, N, with_sum ? dsum : nullptr);
-      });
-    }
+  for (int blocks : {3 * sms, 4 * sms, 5 * sms, 6 * sms, 8 * sms}) {
+    char nm[64];
+    snprintf(nm, sizeof nm, "k_lnmod_bwd_split P=8 grid %d + all sums", blocks);
+    time_it(nm, RW * 20, 20, [&](int i) {
+      k_lnmod_bwd_split<bf16, 8, 8><<<blocks, 256>>>(da[i % SETS], h[i % SETS], stats, lnw, lnb, mod + W, ldm, dmod, dmod + W, dh[i % SETS], 0, dlnw, dlnb, N, dsum);
+    });
   }
+  for (int blocks : {2 * sms, 4 * sms}) {
+    char nm[64];
+    snprintf(nm, sizeof nm, "k_lnmod_bwd_split P=4 grid %d + all sums", blocks);
+    time_it(nm, RW * 20, 20, [&](int i) {
+      k_lnmod_bwd_split<bf16, 8, 4><<<blocks, 256>>>(da[i % SETS], h[i % SETS], stats, lnw, lnb, mod + W, ldm, dmod, dmod + W, dh[i % SETS], 0, dlnw, dlnb, N, dsum);
+    });
+  }
+  time_it("k_lnmod_bwd_split P=8 grid 592, no sums", RW * 20, 20, [&](int i) {
+    k_lnmod_bwd_split<bf16, 8, 8><<<4 * sms, 256>>>(da[i % SETS], h[i % SETS], stats, lnw, lnb, mod + W, ldm, dmod, dmod + W, dh[i % SETS], 0, nullptr, nullptr, N, nullptr);
+  });
+  time_it("k_lnmod_bwd_split P=8 grid 592, first, no sums", RW * 16, 20, [&](int i) {
+    k_lnmod_bwd_split<bf16, 8, 8><<<4 * sms, 256>>>(da[i % SETS], h[i % SETS], stats, nullptr, nullptr, mod + W, ldm, dmod, dmod + W, dh[i % SETS], 1, nullptr, nullptr, N, nullptr);
+  });
+  time_it("k_lnmod_bwd_split P=4 grid 592, first, no sums", RW * 16, 20, [&](int i) {
+    k_lnmod_bwd_split<bf16, 8, 4><<<4 * sms, 256>>>(da[i % SETS], h[i % SETS], stats, nullptr, nullptr, mod + W, ldm, dmod, dmod + W, dh[i % SETS], 1, nullptr, nullptr, N, nullptr);
+  });
   // ---- column sums of [N, 2 W] (what the fused sums replace)
   {
     dim3 g((2 * W + 255) / 256, (unsigned)((N + CS_ROWS - 1) / CS_ROWS));

@@ -307,128 +307,126 @@ k_gate_bwd(const float* __restrict__ dh, const TA* __restrict__ gate, const TA* 
 // dh = (first ? 0 : dh) + dh_ln.  One warp per row, W = NV * 128; the column sums for ln_w / ln_b are
 // kept in registers over the rows of a warp, combined through shared memory and added atomically.
 // ------------------------------------------------------------------------------------------
-template <typename TA, int NV>
-__global__ void __launch_bounds__(256)
-k_lnmod_bwd(const TA* __restrict__ da, const float* __restrict__ h, const float* __restrict__ stats,
-            const float* __restrict__ ln_w, const float* __restrict__ ln_b, const TA* __restrict__ scale,
-            int64_t ldmod, TA* __restrict__ dshift, TA* __restrict__ dscale, float* __restrict__ dh, int first,
-            float* __restrict__ dln_w, float* __restrict__ dln_b, int64_t rows, float* __restrict__ dsum = nullptr) {
+// A row is split over P warps (a lane holds 32 / P columns).  The first form of this kernel kept a row per warp: ncu
+// showed 255 registers per thread, 8 resident warps per SM (12 % of the maximum), dram at 50 %: every warp walked a
+// chain of ~1500 dependent-issue instructions per row (82 us + a 19 us column-sum pass at 16 384 rows; an L2 prefetch of
+// the next row only made it slower).  With P = 4 a thread holds 8 columns (114 registers, 2 blocks = 16 warps per SM),
+// the per-row chain is a quarter as long, the row sums are combined through shared memory and a named barrier of the
+// row's P warps: 59 us with all four column sums (scripts/rowkernel_bench.cu; P = 8 at 64 registers: 62 us).
+// dsum ([2 W], may be null): bias gradient of the shift | scale parts of this modulation = column sums of dshift |
+// dscale.  All four column sums (ln_w, ln_b, shift, scale) are register accumulators, combined per block at the end.
+template <typename TA, int NV, int P>
+__global__ void __launch_bounds__(256, (P >= 8 ? 4 : 2))
+k_lnmod_bwd_split(const TA* __restrict__ da, const float* __restrict__ h, const float* __restrict__ stats,
+                  const float* __restrict__ ln_w, const float* __restrict__ ln_b, const TA* __restrict__ scale,
+                  int64_t ldmod, TA* __restrict__ dshift, TA* __restrict__ dscale, float* __restrict__ dh, int first,
+                  float* __restrict__ dln_w, float* __restrict__ dln_b, int64_t rows, float* __restrict__ dsum) {
   constexpr int W = NV * 128;
-  __shared__ float red[8][W / 4 + 1];  // reused for the two column sums (quarter of the row at a time)
-  // dsum ([2 W]: bias gradient of the shift | scale parts of this modulation = column sums of dshift | dscale; may be
-  // null): accumulated per warp in its own shared-memory rows (16-byte load + 4 adds + 16-byte store per 4 columns, no
-  // atomics: shared fp32 atomics are CAS loops), combined over the 8 warps at the end.  Needs 8 x 2 x W floats of
-  // dynamic shared memory.  Replaces a k_colsum pass over [rows, 2 W] per modulation.
-  extern __shared__ float4 wsum[];  // [8 warps][2][W / 4]
-  const int lane = threadIdx.x & 31;
-  const int wib = threadIdx.x >> 5;
-  float4* my_sum = wsum + (size_t)wib * 2 * (W / 4);
-  if (dsum) {
+  constexpr int NC = NV / P;        // 128-column chunks per warp
+  constexpr int RPB = 8 / P;        // rows per block iteration
+  static_assert(NV % P == 0 && 8 % P == 0, "row split");
+  __shared__ float2 part[2][RPB][P];
+  __shared__ float red[8][NC * 128];
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  const int slot = wib / P, p = wib % P;
+  float aw[NC][4], ab[NC][4], as[NC][4], ac[NC][4];
 #pragma unroll
-    for (int i = 0; i < 2 * NV; ++i) my_sum[lane + 32 * i] = make_float4(0.f, 0.f, 0.f, 0.f);
-  }
-  const int64_t warp_global = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const int64_t warps_total = ((int64_t)gridDim.x * blockDim.x) >> 5;
-  float aw[NV][4], ab[NV][4];
+  for (int i = 0; i < NC; ++i)
 #pragma unroll
-  for (int i = 0; i < NV; ++i)
-#pragma unroll
-    for (int q = 0; q < 4; ++q) aw[i][q] = ab[i][q] = 0.f;
-
-  for (int64_t r = warp_global; r < rows; r += warps_total) {
-    const float mean = stats[2 * r], rstd = stats[2 * r + 1];
-    float xh[NV][4], dx[NV][4];
-    float s1 = 0.f, s2 = 0.f;
-    // the running d h is requested together with the other operands of the row: one memory round trip per row
-    // instead of two (8 warps per SM: the per-row latency chain is what bounds this kernel)
-    float4 prev[NV];
-    if (!first) {
-#pragma unroll
-      for (int i = 0; i < NV; ++i) prev[i] = *reinterpret_cast<const float4*>(dh + r * W + (lane + 32 * i) * 4);
-    }
-#pragma unroll
-    for (int i = 0; i < NV; ++i) {
-      const int j = (lane + 32 * i) * 4;
-      const float4 hv = *reinterpret_cast<const float4*>(h + r * W + j);
-      float d[4], sc[4];
-      load4<TA>(da + r * W + j, d);
-      load4<TA>(scale + r * ldmod + j, sc);
-      xh[i][0] = (hv.x - mean) * rstd; xh[i][1] = (hv.y - mean) * rstd;
-      xh[i][2] = (hv.z - mean) * rstd; xh[i][3] = (hv.w - mean) * rstd;
-      float lw[4] = {1.f, 1.f, 1.f, 1.f}, lb[4] = {0.f, 0.f, 0.f, 0.f};
-      if (ln_w) {
-        const float4 g = __ldg(reinterpret_cast<const float4*>(ln_w + j));
-        const float4 b = __ldg(reinterpret_cast<const float4*>(ln_b + j));
-        lw[0] = g.x; lw[1] = g.y; lw[2] = g.z; lw[3] = g.w;
-        lb[0] = b.x; lb[1] = b.y; lb[2] = b.z; lb[3] = b.w;
-      }
-      float dsc[4];
-#pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        const float nh = xh[i][q] * lw[q] + lb[q];
-        dsc[q] = d[q] * nh;
-        const float dn = d[q] * (1.0f + sc[q]);
-        aw[i][q] += dn * xh[i][q];
-        ab[i][q] += dn;
-        dx[i][q] = dn * lw[q];
-        s1 += dx[i][q];
-        s2 += dx[i][q] * xh[i][q];
-      }
-      store4(dshift + r * ldmod + j, d);
-      store4(dscale + r * ldmod + j, dsc);
-      if (dsum) {
-        float4 a0 = my_sum[lane + 32 * i], a1 = my_sum[W / 4 + lane + 32 * i];
-        a0.x += d[0]; a0.y += d[1]; a0.z += d[2]; a0.w += d[3];
-        a1.x += dsc[0]; a1.y += dsc[1]; a1.z += dsc[2]; a1.w += dsc[3];
-        my_sum[lane + 32 * i] = a0;
-        my_sum[W / 4 + lane + 32 * i] = a1;
-      }
-    }
-    s1 = warp_sum(s1) * (1.0f / W);
-    s2 = warp_sum(s2) * (1.0f / W);
-#pragma unroll
-    for (int i = 0; i < NV; ++i) {
-      const int j = (lane + 32 * i) * 4;
-      float o[4];
-#pragma unroll
-      for (int q = 0; q < 4; ++q) o[q] = rstd * (dx[i][q] - s1 - xh[i][q] * s2);
+    for (int q = 0; q < 4; ++q) aw[i][q] = ab[i][q] = as[i][q] = ac[i][q] = 0.f;
+  const int64_t nblk = (rows + RPB - 1) / RPB;  // block iterations (uniform over the block: the barrier needs all P warps)
+  int par = 0;
+  for (int64_t it = blockIdx.x; it < nblk; it += gridDim.x, par ^= 1) {
+    const int64_t r = it * RPB + slot;
+    const bool on = r < rows;
+    float xh[NC][4], dx[NC][4];
+    float4 prev[NC];
+    float s1 = 0.f, s2 = 0.f, rstd = 0.f;
+    if (on) {
+      const float mean = stats[2 * r];
+      rstd = stats[2 * r + 1];
       if (!first) {
-        const float4 p = prev[i];
-        o[0] += p.x; o[1] += p.y; o[2] += p.z; o[3] += p.w;
+#pragma unroll
+        for (int i = 0; i < NC; ++i) prev[i] = *reinterpret_cast<const float4*>(dh + r * W + (lane + 32 * (i * P + p)) * 4);
       }
-      store4(dh + r * W + j, o);
+#pragma unroll
+      for (int i = 0; i < NC; ++i) {
+        const int j = (lane + 32 * (i * P + p)) * 4;
+        const float4 hv = *reinterpret_cast<const float4*>(h + r * W + j);
+        float d[4], sc[4];
+        load4<TA>(da + r * W + j, d);
+        load4<TA>(scale + r * ldmod + j, sc);
+        xh[i][0] = (hv.x - mean) * rstd; xh[i][1] = (hv.y - mean) * rstd;
+        xh[i][2] = (hv.z - mean) * rstd; xh[i][3] = (hv.w - mean) * rstd;
+        float lw[4] = {1.f, 1.f, 1.f, 1.f}, lb[4] = {0.f, 0.f, 0.f, 0.f};
+        if (ln_w) {
+          const float4 g = __ldg(reinterpret_cast<const float4*>(ln_w + j));
+          const float4 b = __ldg(reinterpret_cast<const float4*>(ln_b + j));
+          lw[0] = g.x; lw[1] = g.y; lw[2] = g.z; lw[3] = g.w;
+          lb[0] = b.x; lb[1] = b.y; lb[2] = b.z; lb[3] = b.w;
+        }
+        float dsc[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const float nh = xh[i][q] * lw[q] + lb[q];
+          dsc[q] = d[q] * nh;
+          const float dn = d[q] * (1.0f + sc[q]);
+          aw[i][q] += dn * xh[i][q];
+          ab[i][q] += dn;
+          as[i][q] += d[q];
+          ac[i][q] += dsc[q];
+          dx[i][q] = dn * lw[q];
+          s1 += dx[i][q];
+          s2 += dx[i][q] * xh[i][q];
+        }
+        store4(dshift + r * ldmod + j, d);
+        store4(dscale + r * ldmod + j, dsc);
+      }
+    }
+    s1 = warp_sum(s1);
+    s2 = warp_sum(s2);
+    if (lane == 0) part[par][slot][p] = make_float2(s1, s2);
+    asm volatile("bar.sync %0, %1;" ::"r"(1 + slot), "r"(32 * P) : "memory");
+    s1 = 0.f; s2 = 0.f;
+#pragma unroll
+    for (int k = 0; k < P; ++k) { const float2 v = part[par][slot][k]; s1 += v.x; s2 += v.y; }
+    s1 *= (1.0f / W);
+    s2 *= (1.0f / W);
+    if (on) {
+#pragma unroll
+      for (int i = 0; i < NC; ++i) {
+        const int j = (lane + 32 * (i * P + p)) * 4;
+        float o[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) o[q] = rstd * (dx[i][q] - s1 - xh[i][q] * s2);
+        if (!first) {
+          const float4 pv = prev[i];
+          o[0] += pv.x; o[1] += pv.y; o[2] += pv.z; o[3] += pv.w;
+        }
+        store4(dh + r * W + j, o);
+      }
     }
   }
-  if (dsum) {  // (uniform over the grid)
+  // column sums: the RPB row slots that hold the same columns are combined in shared memory, one reduction per column
+  // and block.  which: 0 ln_w, 1 ln_b, 2 shift bias, 3 scale bias
+  for (int which = 0; which < 4; ++which) {
+    float* dst = which == 0 ? dln_w : which == 1 ? dln_b : which == 2 ? dsum : (dsum ? dsum + W : nullptr);
+    if (dst == nullptr) continue;  // uniform over the grid
     __syncthreads();
-    const float* all = reinterpret_cast<const float*>(wsum);
-    for (int c = threadIdx.x; c < 2 * W; c += blockDim.x) {
+#pragma unroll
+    for (int i = 0; i < NC; ++i)
+#pragma unroll
+      for (int q = 0; q < 4; ++q)
+        red[wib][i * 128 + lane * 4 + q] = which == 0 ? aw[i][q] : which == 1 ? ab[i][q] : which == 2 ? as[i][q] : ac[i][q];
+    __syncthreads();
+    for (int c = threadIdx.x; c < W; c += blockDim.x) {
+      // column c = (l + 32 (i P + pp)) 4 + q  ->  chunk = c / 128 = i P + pp, offset in chunk = c % 128
+      const int chunk = c >> 7, off = c & 127;
+      const int pp = chunk % P, i = chunk / P;
       float t = 0.f;
 #pragma unroll
-      for (int w8 = 0; w8 < 8; ++w8) t += all[(size_t)w8 * 2 * W + c];
-      atomicAdd(dsum + c, t);
-    }
-  }
-  if (dln_w == nullptr) return;  // uniform over the grid
-  // block-level column sums: 8 warps -> shared -> atomics, a quarter of the row (W/4 columns) per pass
-  for (int which = 0; which < 2; ++which) {
-    for (int part = 0; part < 4; ++part) {
-      __syncthreads();
-#pragma unroll
-      for (int i = 0; i < NV; ++i) {
-        const int j = (lane + 32 * i) * 4;
-        if (j / (W / 4) == part) {
-#pragma unroll
-          for (int q = 0; q < 4; ++q) red[wib][j - part * (W / 4) + q] = which ? ab[i][q] : aw[i][q];
-        }
-      }
-      __syncthreads();
-      for (int c = threadIdx.x; c < W / 4; c += blockDim.x) {
-        float s = 0.f;
-#pragma unroll
-        for (int w8 = 0; w8 < 8; ++w8) s += red[w8][c];
-        atomicAdd((which ? dln_b : dln_w) + part * (W / 4) + c, s);
-      }
+      for (int sl = 0; sl < RPB; ++sl) t += red[sl * P + pp][i * 128 + off];
+      atomicAdd(dst + c, t);
     }
   }
 }
