@@ -240,6 +240,33 @@ def test_full_size_properties(video, mode):
         assert float((gacc.cpu() - 2 * g1[n]).norm() / (2 * g1[n]).norm().clamp_min(1e-20)) <= rel, n
 
 
+def test_wgrad_side_stream_equals_in_order(video, monkeypatch):
+    """loss_bwd with more than 1024 rows runs its W x W weight-gradient GEMMs on the handle's side stream beside the
+    data-gradient chain (UVA_WGRAD_STREAM, default on): same kernels on the same operands, so every gradient equals the
+    in-order run up to the order of the split-K atomics, call after call (a buffer rewritten too early would show up)."""
+    dev, _, P = video
+    N = 3000
+    gen = torch.Generator().manual_seed(5)
+    target = torch.randn(N, 16, generator=gen) * 0.5
+    z = torch.randn(N, 768, generator=gen)
+    mask = (torch.rand(N, generator=gen) > 0.25).float()
+    t = torch.randint(0, 1000, (N,), generator=gen)
+    noise = torch.randn(N, 16, generator=gen)
+    res = {}
+    for flag in ("0", "1"):
+        monkeypatch.setenv("UVA_WGRAD_STREAM", flag)
+        h, names = _head(16, 768, 1024, 6, P, 1, dev)
+        runs = [_run(h, names, P, dev, target, z, mask, t, noise) for _ in range(3)]
+        for l, _, dz, g in runs[1:]:
+            assert float(l) == float(runs[0][0]) and torch.equal(dz, runs[0][2])
+            for k in names:
+                assert float((g[k] - runs[0][3][k]).norm() / runs[0][3][k].norm().clamp_min(1e-20)) <= 1e-5, (flag, k)
+        res[flag] = runs[0]
+    assert float(res["0"][0]) == float(res["1"][0]) and torch.equal(res["0"][2], res["1"][2])
+    for k in names:
+        assert float((res["1"][3][k] - res["0"][3][k]).norm() / res["0"][3][k].norm().clamp_min(1e-20)) <= 1e-5, k
+
+
 def test_module_forward_backward_matches_oracle(video):
     """The drop-in nn.Module: DiffLoss.forward under autograd with the reference's RNG call order
     (randint for t, then randn_like for the noise; DL:51, GD:761)."""
