@@ -112,17 +112,29 @@ k_interp_bwd(const float* __restrict__ d, const float* __restrict__ f2, const fl
 
 // AdaptiveAvgPool(4,4) + ReLU backward on 16 x 16 maps: dconv[img, px, c] = y[img, px, c] > 0 ?
 // dpooled[img, c * 16 + region(px)] / 16 : 0   (px = w * 16 + h, region = (w / 4) * 4 + h / 4)
+// 8 channels (16 bytes of y / dconv) per thread; C % 8 == 0.
 __global__ void k_pool_relu_bwd(const float* __restrict__ dpooled, const bf16* __restrict__ y, bf16* __restrict__ dconv,
                                 int64_t imgs, int C) {
-  const int64_t n = imgs * 256 * C;
+  const int c8 = C / 8;
+  const int64_t n = imgs * 256 * c8;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
-    const int c = (int)(i % C);
-    const int64_t r = i / C;
+    const int c = (int)(i % c8) * 8;
+    const int64_t r = i / c8;
     const int px = (int)(r % 256);
     const int64_t img = r / 256;
     const int reg = ((px >> 4) >> 2) * 4 + ((px & 15) >> 2);
-    const float g = dpooled[img * 16 * C + (int64_t)c * 16 + reg] * 0.0625f;
-    dconv[i] = __float2bfloat16_rn(__bfloat162float(y[i]) > 0.f ? g : 0.f);
+    const uint4 yv = *reinterpret_cast<const uint4*>(y + r * C + c);
+    const __nv_bfloat162* y2 = reinterpret_cast<const __nv_bfloat162*>(&yv);
+    const float* gp = dpooled + img * 16 * C + (int64_t)c * 16 + reg;
+    uint4 ov;
+    uint32_t* o = reinterpret_cast<uint32_t*>(&ov);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const float2 f = __bfloat1622float2(y2[k]);
+      const float g0 = __ldg(gp + (2 * k) * 16) * 0.0625f, g1 = __ldg(gp + (2 * k + 1) * 16) * 0.0625f;
+      o[k] = pack_bf16x2(f.x > 0.f ? g0 : 0.f, f.y > 0.f ? g1 : 0.f);
+    }
+    *reinterpret_cast<uint4*>(dconv + r * C + c) = ov;
   }
 }
 
