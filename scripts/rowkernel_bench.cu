@@ -7,6 +7,7 @@
 #include <vector>
 
 #include "../unified_video_action_b200/csrc/train_bwd_kernels.cuh"
+#include "../unified_video_action_b200/csrc/elementwise.cuh"
 
 using namespace uva;
 
@@ -64,6 +65,19 @@ int main(int argc, char** argv) {
   const double RW = (double)N * W;
   printf("rows %lld, %d SMs, modulation row stride %lld\n", (long long)N, sms, (long long)ldm);
 
+  for (int i = 0; i < 300; ++i) CK(cudaMemcpyAsync(dh[(i + 1) % SETS], dh[i % SETS], N * W * 4, cudaMemcpyDeviceToDevice, 0));  // clock ramp
+  CK(cudaDeviceSynchronize());
+  // ---- sampling row kernels: ys = SiLU(cemb + temb[t]) (reads fp32 h[] as cemb, writes bf16 da[])
+  {
+    float* temb; CK(cudaMalloc(&temb, 1000 * W * 4)); CK(cudaMemset(temb, 0, 1000 * W * 4));
+    for (int mult : {8, 16}) {
+      char nm[64];
+      snprintf(nm, sizeof nm, "k_ysilu grid %d", mult * sms);
+      time_it(nm, RW * 6, 20, [&](int i) { k_ysilu<bf16><<<mult * sms, 256>>>(h[i % SETS], temb, nullptr, 500, da[i % SETS], nullptr, N, W); });
+      snprintf(nm, sizeof nm, "k_ysilu generic form, grid %d x 128", 2 * mult * sms);
+      time_it(nm, RW * 6, 20, [&](int i) { k_ysilu<bf16><<<2 * mult * sms, 128>>>(h[i % SETS], temb, nullptr, 500, da[i % SETS], nullptr, N, W); });
+    }
+  }
   // ---- input_proj weight gradient
   for (int C : {16, 2}) {
     char nm[64];

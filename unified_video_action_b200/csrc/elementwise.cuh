@@ -110,12 +110,47 @@ __global__ void k_convert(const float* __restrict__ src, TO* __restrict__ dst, i
 // 181-183, 271-273).  temb is the [T_train, W] table; the timestep of row r is t_rows[r] when
 // t_rows != null, else t_all.   y_out (optional, TA) keeps y for the backward.
 // ------------------------------------------------------------------------------------------
+// SiLU of the sampling-path row kernels: the bf16 operand takes the one-MUFU form the GEMM epilogues use (the kernel was
+// bound by the ~20 instructions per element of __expf + IEEE division, not by HBM); fp32 mode keeps the accurate form.
+template <typename TA>
+__device__ __forceinline__ float silu_out(float x) {
+  if constexpr (sizeof(TA) == 2) return silu_tanh(x);
+  else return silu_f(x);
+}
+
 template <typename TA>
 __global__ void k_ysilu(const float* __restrict__ cemb, const float* __restrict__ temb,
                         const int64_t* __restrict__ t_rows, int t_all, TA* __restrict__ ys,
                         TA* __restrict__ y_out, int64_t rows, int W) {
   const int wq = W / 4;
   const int64_t n = rows * wq;
+  if (wq == (int)blockDim.x && y_out == nullptr) {
+    // sampling form (one block = one row, two rows per iteration): no 64-bit division per element, both 16-byte loads
+    // of the pair requested together
+    const int j = (int)threadIdx.x * 4;
+    for (int64_t r = blockIdx.x; r < rows; r += 2 * (int64_t)gridDim.x) {
+      const int64_t r2 = r + gridDim.x;
+      const bool two = r2 < rows;
+      const float4 c0 = *reinterpret_cast<const float4*>(cemb + r * W + j);
+      const float4 c1 = two ? *reinterpret_cast<const float4*>(cemb + r2 * W + j) : make_float4(0.f, 0.f, 0.f, 0.f);
+      const int64_t t0 = t_rows ? t_rows[r] : (int64_t)t_all;
+      const int64_t t1 = (t_rows && two) ? t_rows[r2] : t0;
+      const float4 e0 = __ldg(reinterpret_cast<const float4*>(temb + t0 * W + j));
+      const float4 e1 = __ldg(reinterpret_cast<const float4*>(temb + t1 * W + j));
+      TA o[4];
+      o[0] = from_f32<TA>(silu_out<TA>(c0.x + e0.x)); o[1] = from_f32<TA>(silu_out<TA>(c0.y + e0.y));
+      o[2] = from_f32<TA>(silu_out<TA>(c0.z + e0.z)); o[3] = from_f32<TA>(silu_out<TA>(c0.w + e0.w));
+      if constexpr (sizeof(TA) == 2) *reinterpret_cast<uint2*>(ys + r * W + j) = *reinterpret_cast<uint2*>(o);
+      else *reinterpret_cast<float4*>(ys + r * W + j) = *reinterpret_cast<float4*>(o);
+      if (two) {
+        o[0] = from_f32<TA>(silu_out<TA>(c1.x + e1.x)); o[1] = from_f32<TA>(silu_out<TA>(c1.y + e1.y));
+        o[2] = from_f32<TA>(silu_out<TA>(c1.z + e1.z)); o[3] = from_f32<TA>(silu_out<TA>(c1.w + e1.w));
+        if constexpr (sizeof(TA) == 2) *reinterpret_cast<uint2*>(ys + r2 * W + j) = *reinterpret_cast<uint2*>(o);
+        else *reinterpret_cast<float4*>(ys + r2 * W + j) = *reinterpret_cast<float4*>(o);
+      }
+    }
+    return;
+  }
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
        i += (int64_t)gridDim.x * blockDim.x) {
     const int64_t r = i / wq;
@@ -132,7 +167,7 @@ __global__ void k_ysilu(const float* __restrict__ cemb, const float* __restrict_
       else *reinterpret_cast<float4*>(y_out + r * W + j) = *reinterpret_cast<float4*>(o);
     }
 #pragma unroll
-    for (int q = 0; q < 4; ++q) o[q] = from_f32<TA>(silu_f(y[q]));
+    for (int q = 0; q < 4; ++q) o[q] = from_f32<TA>(y_out ? silu_f(y[q]) : silu_out<TA>(y[q]));  // (training keeps the accurate form)
     if constexpr (sizeof(TA) == 2) {
       *reinterpret_cast<uint2*>(ys + r * W + j) = *reinterpret_cast<uint2*>(o);
     } else {
@@ -158,8 +193,8 @@ __global__ void k_ysilu_steps(const float* __restrict__ cemb, const float* __res
     const int64_t t = tsteps[k0 + g];
     const float4 c = *reinterpret_cast<const float4*>(cemb + r * W + j);
     const float4 e = __ldg(reinterpret_cast<const float4*>(temb + t * W + j));
-    bf16 o[4] = {__float2bfloat16_rn(silu_f(c.x + e.x)), __float2bfloat16_rn(silu_f(c.y + e.y)),
-                 __float2bfloat16_rn(silu_f(c.z + e.z)), __float2bfloat16_rn(silu_f(c.w + e.w))};
+    bf16 o[4] = {__float2bfloat16_rn(silu_tanh(c.x + e.x)), __float2bfloat16_rn(silu_tanh(c.y + e.y)),
+                 __float2bfloat16_rn(silu_tanh(c.z + e.z)), __float2bfloat16_rn(silu_tanh(c.w + e.w))};
     *reinterpret_cast<uint2*>(ys + ((int64_t)g * rows + r) * W + j) = *reinterpret_cast<uint2*>(o);
   }
 }
