@@ -267,6 +267,34 @@ def test_wgrad_side_stream_equals_in_order(video, monkeypatch):
         assert float((res["1"][3][k] - res["0"][3][k]).norm() / res["0"][3][k].norm().clamp_min(1e-20)) <= 1e-5, k
 
 
+@pytest.mark.parametrize("switch,tol", [("UVA_FUSE_COLSUM", 5e-3), ("UVA_EPI_COLSUM", 5e-3), ("UVA_FINAL_TC", BF16_GRAD_L2)])
+def test_backward_switches_off_equal_default(video, monkeypatch, switch, tol):
+    """The fused forms of the backward keep their unfused fallbacks behind switches: bias
+    gradients summed inside k_gate_bwd / k_lnmod_bwd_split vs separate k_colsum passes (UVA_FUSE_COLSUM), inside the SiLU'
+    GEMM epilogue vs a pass (UVA_EPI_COLSUM), final-layer backward on tcgen05 vs CUDA cores (UVA_FINAL_TC: the tcgen05 form
+    rounds d loss / d net to bf16, hence the bf16 gradient tolerance).  Same gradients either way; the fused bias sums
+    add the fp32 values BEFORE they are rounded to the bf16 operand the separate pass reads, so the two differ by that
+    rounding (measured 1.4e-3 on mlp.2.bias at 2500 rows; bound 5e-3)."""
+    dev, _, P = video
+    N = 2500
+    gen = torch.Generator().manual_seed(9)
+    target = torch.randn(N, 16, generator=gen) * 0.5
+    z = torch.randn(N, 768, generator=gen)
+    mask = (torch.rand(N, generator=gen) > 0.25).float()
+    t = torch.randint(0, 1000, (N,), generator=gen)
+    noise = torch.randn(N, 16, generator=gen)
+    res = {}
+    for flag in ("1", "0"):
+        monkeypatch.setenv(switch, flag)
+        h, names = _head(16, 768, 1024, 6, P, 1, dev)
+        res[flag] = _run(h, names, P, dev, target, z, mask, t, noise)
+    assert float(res["0"][0]) == float(res["1"][0])
+    assert float((res["0"][2] - res["1"][2]).norm() / res["1"][2].norm()) <= tol
+    for k in names:
+        a, b = res["0"][3][k], res["1"][3][k]
+        assert float((a - b).norm() / b.norm().clamp_min(1e-20)) <= tol, (switch, k)
+
+
 def test_module_forward_backward_matches_oracle(video):
     """The drop-in nn.Module: DiffLoss.forward under autograd with the reference's RNG call order
     (randint for t, then randn_like for the noise; DL:51, GD:761)."""
