@@ -513,20 +513,24 @@ __global__ void k_philox_fill(PhiloxSeed s, uint32_t step0, int64_t per_step, in
 // `noise[e]`, or Philox element e): learned-range variance GD:283-291, x0-from-eps GD:348-353 (+ clip GD:293-297),
 // posterior mean GD:238-258, ancestral step GD:431-444 with the temperature scaling.  Shared by k_ddpm_step and
 // the fused final-layer epilogue (final_ddpm.cuh) so that both give the same bits.
-__device__ __forceinline__ float ddpm_update(float eps, float v, float x, const float* __restrict__ noise,
-                                             const PhiloxSeed& ps, uint32_t step, int64_t e, float temperature,
-                                             int clip, const StepCoef& k) {
+// (the arithmetic, with the noise draw nz already in hand: ddpm_update and the vectorised epilogue of final_ddpm.cuh share it)
+__device__ __forceinline__ float ddpm_update_nz(float eps, float v, float x, float nz, float temperature, int clip,
+                                                const StepCoef& k) {
   const float frac = (v + 1.0f) / 2.0f;
   const float logvar = frac * k.max_log + (1.0f - frac) * k.min_log;
   float x0 = k.sqrt_recip * x - k.sqrt_recipm1 * eps;
   if (clip) x0 = fminf(fmaxf(x0, -1.0f), 1.0f);
   const float mean = k.coef1 * x0 + k.coef2 * x;
   float out = mean;
-  if (k.nonzero) {
-    const float nz = ps.on ? philox_normal(ps, step, (uint64_t)e) : noise[e];
-    out = mean + expf(0.5f * logvar) * nz * temperature;
-  }
+  if (k.nonzero) out = mean + expf(0.5f * logvar) * nz * temperature;
   return out;
+}
+__device__ __forceinline__ float ddpm_update(float eps, float v, float x, const float* __restrict__ noise,
+                                             const PhiloxSeed& ps, uint32_t step, int64_t e, float temperature,
+                                             int clip, const StepCoef& k) {
+  float nz = 0.f;
+  if (k.nonzero) nz = ps.on ? philox_normal(ps, step, (uint64_t)e) : noise[e];
+  return ddpm_update_nz(eps, v, x, nz, temperature, clip, k);
 }
 
 __global__ void k_ddpm_step(const float* __restrict__ net, int ldn, const float* __restrict__ x_cur,

@@ -146,9 +146,36 @@ umma_final_ddpm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
     float b[FD_BN];
 #pragma unroll
     for (int i = 0; i < FD_BN; ++i) b[i] = (i < 2 * C) ? __ldg(p.bias + i) : 0.f;
+    const bool vec_ok = (((uintptr_t)p.x_cur | (uintptr_t)p.x_next | (uintptr_t)(p.ps.on ? nullptr : p.noise)) & 15u) == 0;
     for (int64_t item = blockIdx.x; item < items; item += gridDim.x) {
       const int64_t r = item * UG_BM + q * 32 + lane;  // cond row (CFG) / row
       const bool ok = r < span;
+      // C = 16 with 16-byte aligned rows: the row's state (and its noise draws, when they come from memory) are requested
+      // as 16-byte loads BEFORE the accumulator is waited for, and the result leaves as 16-byte stores.  The element-wise
+      // form below walks 16 channels x (load x, load noise, store) one dependent global access after the other:
+      // ~30 us per item for an item whose operands arrive in ~6 us (ncu: dram 29 %, sm 8 %)
+      const bool vec = (C == 16) && ok && vec_ok;
+      float4 xr0[4], xr1[4], nr0[4], nr1[4];
+      if (vec) {
+        const float4* px0 = reinterpret_cast<const float4*>(p.x_cur + r * 16);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) xr0[i] = px0[i];
+        if constexpr (CFG) {
+          const float4* px1 = reinterpret_cast<const float4*>(p.x_cur + (r + p.half) * 16);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) xr1[i] = px1[i];
+        }
+        if (p.kc.nonzero && !p.ps.on) {
+          const float4* pn0 = reinterpret_cast<const float4*>(p.noise + (p.g0 + r) * 16);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) nr0[i] = pn0[i];
+          if constexpr (CFG) {
+            const float4* pn1 = reinterpret_cast<const float4*>(p.noise + (p.g0 + p.ghalf + r) * 16);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) nr1[i] = pn1[i];
+          }
+        }
+      }
       mbar_wait(&tfull_bar[acc], acc_phase);
       tc_fence_after();
       const uint32_t t_addr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * Cfg::kAccCols);
@@ -159,7 +186,40 @@ umma_final_ddpm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tempty_bar[acc]);  // the accumulator is in registers now
-      if (ok) {
+      if (vec) {
+        const float* x0 = reinterpret_cast<const float*>(xr0);
+        const float* x1 = reinterpret_cast<const float*>(xr1);
+        const float* n0 = reinterpret_cast<const float*>(nr0);
+        const float* n1 = reinterpret_cast<const float*>(nr1);
+        float o0[16], o1[16];
+#pragma unroll
+        for (int c = 0; c < 16; ++c) {
+          const float ce = __uint_as_float(v0[c]) + b[c], cv = __uint_as_float(v0[16 + c]) + b[16 + c];
+          if constexpr (CFG) {
+            const float ue = __uint_as_float(v1[c]) + b[c], uv = __uint_as_float(v1[16 + c]) + b[16 + c];
+            const float eps = ue + p.cfg * (ce - ue);
+            float z0 = 0.f, z1 = 0.f;
+            if (p.kc.nonzero) {
+              z0 = p.ps.on ? philox_normal(p.ps, p.step, (uint64_t)((p.g0 + r) * 16 + c)) : n0[c];
+              z1 = p.ps.on ? philox_normal(p.ps, p.step, (uint64_t)((p.g0 + p.ghalf + r) * 16 + c)) : n1[c];
+            }
+            o0[c] = ddpm_update_nz(eps, cv, x0[c], z0, p.temperature, p.clip, p.kc);
+            o1[c] = ddpm_update_nz(eps, uv, x1[c], z1, p.temperature, p.clip, p.kc);
+          } else {
+            float z0 = 0.f;
+            if (p.kc.nonzero) z0 = p.ps.on ? philox_normal(p.ps, p.step, (uint64_t)((p.g0 + r) * 16 + c)) : n0[c];
+            o0[c] = ddpm_update_nz(ce, cv, x0[c], z0, p.temperature, p.clip, p.kc);
+          }
+        }
+        float4* po0 = reinterpret_cast<float4*>(p.x_next + r * 16);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) po0[i] = make_float4(o0[4 * i], o0[4 * i + 1], o0[4 * i + 2], o0[4 * i + 3]);
+        if constexpr (CFG) {
+          float4* po1 = reinterpret_cast<float4*>(p.x_next + (r + p.half) * 16);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) po1[i] = make_float4(o1[4 * i], o1[4 * i + 1], o1[4 * i + 2], o1[4 * i + 3]);
+        }
+      } else if (ok) {
 #pragma unroll
         for (int c = 0; c < FD_BN / 2; ++c) {
           if (c < C) {
