@@ -682,3 +682,26 @@ def test_hoist_overlap_equals_serial_hoist(video, monkeypatch, N, cfg):
         assert torch.isfinite(calls[0]).all()
         outs[flag] = calls[0]
     assert torch.equal(outs["0"], outs["1"])
+
+
+def test_final_ddpm_epilogue_unaligned_noise_pointer(video):
+    """The fused final layer reads the row state and the noise with 16-byte loads when the pointers allow it; a noise
+    tensor that starts 4 bytes off a 16-byte boundary (a contiguous view of a larger buffer) takes the element-wise
+    form of the same epilogue: same bits."""
+    dev, g, P = video
+    h = _head(16, 768, 1024, 6, P, 1, dev)
+    gen = torch.Generator().manual_seed(61)
+    for N, cfg, k_end in ((6000, 3.0, 2), (300, 1.0, 5)):
+        z = torch.randn(N, 768, generator=gen).to(dev)
+        x0 = torch.randn(N, 16, generator=gen).to(dev)
+        if cfg != 1.0:
+            x0[N // 2:] = x0[:N // 2]
+        nz = torch.randn(k_end, N, 16, generator=gen).to(dev)
+        buf = torch.empty(nz.numel() + 1, device=dev)
+        off = buf[1:].view(k_end, N, 16)
+        off.copy_(nz)
+        assert off.data_ptr() % 16 == 4 and off.is_contiguous()
+        a = h.sample(z, x0, nz, temperature=0.95, cfg=cfg, k_begin=0, k_end=k_end).clone()
+        b = h.sample(z, x0, off, temperature=0.95, cfg=cfg, k_begin=0, k_end=k_end).clone()
+        torch.cuda.synchronize()
+        assert torch.equal(a, b), (N, float((a - b).abs().max()))
