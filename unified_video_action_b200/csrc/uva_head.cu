@@ -271,6 +271,7 @@ struct UvaHead {
   // chain) run on hoist_st beside the data-gradient GEMMs and row kernels of the chain, which wait for them only
   // before their operand buffer is rewritten one block later (measured, C2 step, 4 A/B pairs: 5.23 -> 5.06 ms)
   bool wgrad_stream = true;
+  int wgrad_side_mult = 1;  // UVA_WGRAD_SIDE_MULT: grid multiplier of the side-stream weight-gradient GEMMs (4 = one item per cluster: measured 5.07 vs 5.03 ms, no gain)
   cudaEvent_t ev_wfork = nullptr, ev_w1 = nullptr, ev_w2 = nullptr;
   bool bn32 = true;              // UVA_BN32: 128 x 32 tiles for the W x W GEMMs when rows <= 128 (32 CTAs stream the weight)
   struct SmallGraph {
@@ -434,6 +435,7 @@ extern "C" int uva_head_create(const UvaHeadDesc* desc, UvaHead** out) {
   if (const char* e = getenv("UVA_HOIST_OVERLAP")) h->hoist_overlap = atoi(e) != 0;
   if (const char* e = getenv("UVA_HOIST_SMS")) h->hoist_sms = atoi(e);
   if (const char* e = getenv("UVA_WGRAD_STREAM")) h->wgrad_stream = atoi(e) != 0;
+  if (const char* e = getenv("UVA_WGRAD_SIDE_MULT")) { int v = atoi(e); if (v >= 1 && v <= 64) h->wgrad_side_mult = v; }
   if (const char* e = getenv("UVA_FINAL_TC")) h->final_tc = atoi(e) != 0;
   if (const char* e = getenv("UVA_TRAIN_GRAPH")) h->train_graph = atoi(e) != 0;
   if (const char* e = getenv("UVA_TRAIN_GRAPH_ROWS")) h->train_graph_rows = atol(e);
