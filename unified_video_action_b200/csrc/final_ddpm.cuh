@@ -150,29 +150,45 @@ umma_final_ddpm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
     for (int64_t item = blockIdx.x; item < items; item += gridDim.x) {
       const int64_t r = item * UG_BM + q * 32 + lane;  // cond row (CFG) / row
       const bool ok = r < span;
-      // C = 16 with 16-byte aligned rows: the row's state (and its noise draws, when they come from memory) are requested
-      // as 16-byte loads BEFORE the accumulator is waited for, and the result leaves as 16-byte stores.  The element-wise
-      // form below walks 16 channels x (load x, load noise, store) one dependent global access after the other:
-      // ~30 us per item for an item whose operands arrive in ~6 us (ncu: dram 29 %, sm 8 %)
-      const bool vec = (C == 16) && ok && vec_ok;
-      float4 xr0[4], xr1[4], nr0[4], nr1[4];
-      if (vec) {
-        const float4* px0 = reinterpret_cast<const float4*>(p.x_cur + r * 16);
+      // The row's state (and its noise draws, when they come from memory) are requested BEFORE the accumulator is waited
+      // for - as 16-byte loads when C = 16 and the pointers allow it, as independent 4-byte loads otherwise - and the
+      // result leaves as 16-byte (or independent 4-byte) stores.  The first form of this epilogue walked the channels
+      // one dependent global access after the other (load x, load noise, store): ~30 us per 128-row item at C = 16 for an
+      // item whose operands arrive in ~6 us (ncu: dram 29 %, sm 8 %)
+      const bool vec = (C == 16) && vec_ok;
+      const bool mem_noise = p.kc.nonzero && !p.ps.on;
+      float x0[16], x1[16], n0[16], n1[16];
+      if (ok) {
+        if (vec) {
+          const float4* px0 = reinterpret_cast<const float4*>(p.x_cur + r * 16);
 #pragma unroll
-        for (int i = 0; i < 4; ++i) xr0[i] = px0[i];
-        if constexpr (CFG) {
-          const float4* px1 = reinterpret_cast<const float4*>(p.x_cur + (r + p.half) * 16);
-#pragma unroll
-          for (int i = 0; i < 4; ++i) xr1[i] = px1[i];
-        }
-        if (p.kc.nonzero && !p.ps.on) {
-          const float4* pn0 = reinterpret_cast<const float4*>(p.noise + (p.g0 + r) * 16);
-#pragma unroll
-          for (int i = 0; i < 4; ++i) nr0[i] = pn0[i];
+          for (int i = 0; i < 4; ++i) { const float4 t = px0[i]; x0[4 * i] = t.x; x0[4 * i + 1] = t.y; x0[4 * i + 2] = t.z; x0[4 * i + 3] = t.w; }
           if constexpr (CFG) {
-            const float4* pn1 = reinterpret_cast<const float4*>(p.noise + (p.g0 + p.ghalf + r) * 16);
+            const float4* px1 = reinterpret_cast<const float4*>(p.x_cur + (r + p.half) * 16);
 #pragma unroll
-            for (int i = 0; i < 4; ++i) nr1[i] = pn1[i];
+            for (int i = 0; i < 4; ++i) { const float4 t = px1[i]; x1[4 * i] = t.x; x1[4 * i + 1] = t.y; x1[4 * i + 2] = t.z; x1[4 * i + 3] = t.w; }
+          }
+          if (mem_noise) {
+            const float4* pn0 = reinterpret_cast<const float4*>(p.noise + (p.g0 + r) * 16);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) { const float4 t = pn0[i]; n0[4 * i] = t.x; n0[4 * i + 1] = t.y; n0[4 * i + 2] = t.z; n0[4 * i + 3] = t.w; }
+            if constexpr (CFG) {
+              const float4* pn1 = reinterpret_cast<const float4*>(p.noise + (p.g0 + p.ghalf + r) * 16);
+#pragma unroll
+              for (int i = 0; i < 4; ++i) { const float4 t = pn1[i]; n1[4 * i] = t.x; n1[4 * i + 1] = t.y; n1[4 * i + 2] = t.z; n1[4 * i + 3] = t.w; }
+            }
+          }
+        } else {
+#pragma unroll
+          for (int c = 0; c < 16; ++c) {
+            if (c < C) {
+              x0[c] = p.x_cur[r * C + c];
+              if constexpr (CFG) x1[c] = p.x_cur[(r + p.half) * C + c];
+              if (mem_noise) {
+                n0[c] = p.noise[(p.g0 + r) * C + c];
+                if constexpr (CFG) n1[c] = p.noise[(p.g0 + p.ghalf + r) * C + c];
+              }
+            }
           }
         }
       }
@@ -186,40 +202,8 @@ umma_final_ddpm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tempty_bar[acc]);  // the accumulator is in registers now
-      if (vec) {
-        const float* x0 = reinterpret_cast<const float*>(xr0);
-        const float* x1 = reinterpret_cast<const float*>(xr1);
-        const float* n0 = reinterpret_cast<const float*>(nr0);
-        const float* n1 = reinterpret_cast<const float*>(nr1);
+      if (ok) {
         float o0[16], o1[16];
-#pragma unroll
-        for (int c = 0; c < 16; ++c) {
-          const float ce = __uint_as_float(v0[c]) + b[c], cv = __uint_as_float(v0[16 + c]) + b[16 + c];
-          if constexpr (CFG) {
-            const float ue = __uint_as_float(v1[c]) + b[c], uv = __uint_as_float(v1[16 + c]) + b[16 + c];
-            const float eps = ue + p.cfg * (ce - ue);
-            float z0 = 0.f, z1 = 0.f;
-            if (p.kc.nonzero) {
-              z0 = p.ps.on ? philox_normal(p.ps, p.step, (uint64_t)((p.g0 + r) * 16 + c)) : n0[c];
-              z1 = p.ps.on ? philox_normal(p.ps, p.step, (uint64_t)((p.g0 + p.ghalf + r) * 16 + c)) : n1[c];
-            }
-            o0[c] = ddpm_update_nz(eps, cv, x0[c], z0, p.temperature, p.clip, p.kc);
-            o1[c] = ddpm_update_nz(eps, uv, x1[c], z1, p.temperature, p.clip, p.kc);
-          } else {
-            float z0 = 0.f;
-            if (p.kc.nonzero) z0 = p.ps.on ? philox_normal(p.ps, p.step, (uint64_t)((p.g0 + r) * 16 + c)) : n0[c];
-            o0[c] = ddpm_update_nz(ce, cv, x0[c], z0, p.temperature, p.clip, p.kc);
-          }
-        }
-        float4* po0 = reinterpret_cast<float4*>(p.x_next + r * 16);
-#pragma unroll
-        for (int i = 0; i < 4; ++i) po0[i] = make_float4(o0[4 * i], o0[4 * i + 1], o0[4 * i + 2], o0[4 * i + 3]);
-        if constexpr (CFG) {
-          float4* po1 = reinterpret_cast<float4*>(p.x_next + (r + p.half) * 16);
-#pragma unroll
-          for (int i = 0; i < 4; ++i) po1[i] = make_float4(o1[4 * i], o1[4 * i + 1], o1[4 * i + 2], o1[4 * i + 3]);
-        }
-      } else if (ok) {
 #pragma unroll
         for (int c = 0; c < FD_BN / 2; ++c) {
           if (c < C) {
@@ -230,14 +214,35 @@ umma_final_ddpm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
               if (j == c) { ce = __uint_as_float(v0[j]) + b[j]; if constexpr (CFG) ue = __uint_as_float(v1[j]) + b[j]; }
               if (j == C + c) { cv = __uint_as_float(v0[j]) + b[j]; if constexpr (CFG) uv = __uint_as_float(v1[j]) + b[j]; }
             }
+            float z0 = 0.f, z1 = 0.f;
+            if (p.kc.nonzero) {
+              z0 = p.ps.on ? philox_normal(p.ps, p.step, (uint64_t)((p.g0 + r) * C + c)) : n0[c];
+              if constexpr (CFG) z1 = p.ps.on ? philox_normal(p.ps, p.step, (uint64_t)((p.g0 + p.ghalf + r) * C + c)) : n1[c];
+            }
             if constexpr (CFG) {
               const float eps = ue + p.cfg * (ce - ue);
-              const int64_t i0 = r * C + c, i1 = (r + p.half) * C + c;
-              p.x_next[i0] = ddpm_update(eps, cv, p.x_cur[i0], p.noise, p.ps, p.step, (p.g0 + r) * C + c, p.temperature, p.clip, p.kc);
-              p.x_next[i1] = ddpm_update(eps, uv, p.x_cur[i1], p.noise, p.ps, p.step, (p.g0 + p.ghalf + r) * C + c, p.temperature, p.clip, p.kc);
+              o0[c] = ddpm_update_nz(eps, cv, x0[c], z0, p.temperature, p.clip, p.kc);
+              o1[c] = ddpm_update_nz(eps, uv, x1[c], z1, p.temperature, p.clip, p.kc);
             } else {
-              const int64_t i0 = r * C + c;
-              p.x_next[i0] = ddpm_update(ce, cv, p.x_cur[i0], p.noise, p.ps, p.step, (p.g0 + r) * C + c, p.temperature, p.clip, p.kc);
+              o0[c] = ddpm_update_nz(ce, cv, x0[c], z0, p.temperature, p.clip, p.kc);
+            }
+          }
+        }
+        if (vec) {
+          float4* po0 = reinterpret_cast<float4*>(p.x_next + r * 16);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) po0[i] = make_float4(o0[4 * i], o0[4 * i + 1], o0[4 * i + 2], o0[4 * i + 3]);
+          if constexpr (CFG) {
+            float4* po1 = reinterpret_cast<float4*>(p.x_next + (r + p.half) * 16);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) po1[i] = make_float4(o1[4 * i], o1[4 * i + 1], o1[4 * i + 2], o1[4 * i + 3]);
+          }
+        } else {
+#pragma unroll
+          for (int c = 0; c < 16; ++c) {
+            if (c < C) {
+              p.x_next[r * C + c] = o0[c];
+              if constexpr (CFG) p.x_next[(r + p.half) * C + c] = o1[c];
             }
           }
         }
