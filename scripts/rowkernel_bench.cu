@@ -121,6 +121,20 @@ int main(int argc, char** argv) {
       k_lnmod_bwd_split<bf16, 8, 4><<<blocks, 256>>>(da[i % SETS], h[i % SETS], stats, lnw, lnb, mod + W, ldm, dmod, dmod + W, dh[i % SETS], 0, dlnw, dlnb, N, dsum);
     });
   }
+  for (int blocks : {2 * sms, 3 * sms, 4 * sms}) {
+    char nm[80];
+    GateNext<bf16> gn{mod + 2 * W, q[0], dq[0], dmod + 2 * W, sdq, sdg};
+    snprintf(nm, sizeof nm, "k_lnmod_bwd_split P=8 + gate backward, grid %d", blocks);
+    time_it(nm, RW * 28, 20, [&](int i) {
+      gn.q = q[i % SETS]; gn.dq = dq[i % SETS];
+      k_lnmod_bwd_split<bf16, 8, 8, true><<<blocks, 256>>>(da[i % SETS], h[i % SETS], stats, lnw, lnb, mod + W, ldm, dmod + 3 * W, dmod + 4 * W, dh[i % SETS], 0, dlnw, dlnb, N, dsum, gn);
+    });
+    snprintf(nm, sizeof nm, "k_lnmod_bwd_split P=4 + gate backward, grid %d", blocks);
+    time_it(nm, RW * 28, 20, [&](int i) {
+      gn.q = q[i % SETS]; gn.dq = dq[i % SETS];
+      k_lnmod_bwd_split<bf16, 8, 4, true><<<blocks, 256>>>(da[i % SETS], h[i % SETS], stats, lnw, lnb, mod + W, ldm, dmod + 3 * W, dmod + 4 * W, dh[i % SETS], 0, dlnw, dlnb, N, dsum, gn);
+    });
+  }
   time_it("k_lnmod_bwd_split P=8 grid 592, no sums", RW * 20, 20, [&](int i) {
     k_lnmod_bwd_split<bf16, 8, 8><<<4 * sms, 256>>>(da[i % SETS], h[i % SETS], stats, lnw, lnb, mod + W, ldm, dmod, dmod + W, dh[i % SETS], 0, nullptr, nullptr, N, nullptr);
   });

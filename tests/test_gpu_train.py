@@ -267,11 +267,14 @@ def test_wgrad_side_stream_equals_in_order(video, monkeypatch):
         assert float((res["1"][3][k] - res["0"][3][k]).norm() / res["0"][3][k].norm().clamp_min(1e-20)) <= 1e-5, k
 
 
-@pytest.mark.parametrize("switch,tol", [("UVA_FUSE_COLSUM", 5e-3), ("UVA_EPI_COLSUM", 5e-3), ("UVA_FINAL_TC", BF16_GRAD_L2)])
+@pytest.mark.parametrize("switch,tol", [("UVA_FUSE_COLSUM", 5e-3), ("UVA_EPI_COLSUM", 5e-3), ("UVA_FINAL_TC", BF16_GRAD_L2),
+                                        ("UVA_FUSE_GATE_LN", 1e-5)])
 def test_backward_switches_off_equal_default(video, monkeypatch, switch, tol):
     """The fused forms of the backward keep their unfused fallbacks behind switches: bias
     gradients summed inside k_gate_bwd / k_lnmod_bwd_split vs separate k_colsum passes (UVA_FUSE_COLSUM), inside the SiLU'
-    GEMM epilogue vs a pass (UVA_EPI_COLSUM), final-layer backward on tcgen05 vs CUDA cores (UVA_FINAL_TC: the tcgen05 form
+    GEMM epilogue vs a pass (UVA_EPI_COLSUM), the gated-residual backward inside the LayerNorm-modulate backward of the
+    block above vs its own kernel (UVA_FUSE_GATE_LN: same values, only the order of two bias sums differs), final-layer
+    backward on tcgen05 vs CUDA cores (UVA_FINAL_TC: the tcgen05 form
     rounds d loss / d net to bf16, hence the bf16 gradient tolerance).  Same gradients either way; the fused bias sums
     add the fp32 values BEFORE they are rounded to the bf16 operand the separate pass reads, so the two differ by that
     rounding (measured 1.4e-3 on mlp.2.bias at 2500 rows; bound 5e-3)."""

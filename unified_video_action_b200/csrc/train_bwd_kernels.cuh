@@ -315,12 +315,26 @@ k_gate_bwd(const float* __restrict__ dh, const TA* __restrict__ gate, const TA* 
 // row's P warps: 59 us with all four column sums (scripts/rowkernel_bench.cu; P = 8 at 64 registers: 62 us).
 // dsum ([2 W], may be null): bias gradient of the shift | scale parts of this modulation = column sums of dshift |
 // dscale.  All four column sums (ln_w, ln_b, shift, scale) are register accumulators, combined per block at the end.
-template <typename TA, int NV, int P>
-__global__ void __launch_bounds__(256, (P >= 8 ? 4 : 2))
+// GATE: the gated-residual backward of the NEXT block down the stack (k_gate_bwd: dq = dh * gate, dgate = dh * q, and their
+// column sums) rides along: the d h row this kernel has just produced is still in registers, so the separate kernel's
+// re-read of it (4 of its 12 bytes per element) and its launch disappear.
+template <typename TA>
+struct GateNext {
+  const TA* gate;    // [rows, ldmod] gate third of the next block's modulation
+  const TA* q;       // [rows, W] that block's mlp output before the gate
+  TA* dq;            // [rows, W]
+  TA* dgate;         // [rows, ldmod]
+  float* sum_dq;     // [W] += column sums of dq (mlp.2 bias gradient), may be null
+  float* sum_dgate;  // [W] += column sums of dgate (gate third of the adaLN bias gradient), may be null
+};
+
+template <typename TA, int NV, int P, bool GATE = false>
+__global__ void __launch_bounds__(256, (P >= 8 ? (GATE ? 3 : 4) : 2))
 k_lnmod_bwd_split(const TA* __restrict__ da, const float* __restrict__ h, const float* __restrict__ stats,
                   const float* __restrict__ ln_w, const float* __restrict__ ln_b, const TA* __restrict__ scale,
                   int64_t ldmod, TA* __restrict__ dshift, TA* __restrict__ dscale, float* __restrict__ dh, int first,
-                  float* __restrict__ dln_w, float* __restrict__ dln_b, int64_t rows, float* __restrict__ dsum) {
+                  float* __restrict__ dln_w, float* __restrict__ dln_b, int64_t rows, float* __restrict__ dsum,
+                  GateNext<TA> gn = GateNext<TA>{}) {
   constexpr int W = NV * 128;
   constexpr int NC = NV / P;        // 128-column chunks per warp
   constexpr int RPB = 8 / P;        // rows per block iteration
@@ -330,10 +344,15 @@ k_lnmod_bwd_split(const TA* __restrict__ da, const float* __restrict__ h, const 
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   const int slot = wib / P, p = wib % P;
   float aw[NC][4], ab[NC][4], as[NC][4], ac[NC][4];
+  float aq[GATE ? NC : 1][4], ag[GATE ? NC : 1][4];
 #pragma unroll
   for (int i = 0; i < NC; ++i)
 #pragma unroll
     for (int q = 0; q < 4; ++q) aw[i][q] = ab[i][q] = as[i][q] = ac[i][q] = 0.f;
+#pragma unroll
+  for (int i = 0; i < (GATE ? NC : 1); ++i)
+#pragma unroll
+    for (int q = 0; q < 4; ++q) aq[i][q] = ag[i][q] = 0.f;
   const int64_t nblk = (rows + RPB - 1) / RPB;  // block iterations (uniform over the block: the barrier needs all P warps)
   int par = 0;
   for (int64_t it = blockIdx.x; it < nblk; it += gridDim.x, par ^= 1) {
@@ -341,10 +360,19 @@ k_lnmod_bwd_split(const TA* __restrict__ da, const float* __restrict__ h, const 
     const bool on = r < rows;
     float xh[NC][4], dx[NC][4];
     float4 prev[NC];
+    float gt[GATE ? NC : 1][4], qn[GATE ? NC : 1][4];
     float s1 = 0.f, s2 = 0.f, rstd = 0.f;
     if (on) {
       const float mean = stats[2 * r];
       rstd = stats[2 * r + 1];
+      if constexpr (GATE) {  // requested with the other operands of the row
+#pragma unroll
+        for (int i = 0; i < NC; ++i) {
+          const int j = (lane + 32 * (i * P + p)) * 4;
+          load4<TA>(gn.gate + r * ldmod + j, gt[i]);
+          load4<TA>(gn.q + r * W + j, qn[i]);
+        }
+      }
       if (!first) {
 #pragma unroll
         for (int i = 0; i < NC; ++i) prev[i] = *reinterpret_cast<const float4*>(dh + r * W + (lane + 32 * (i * P + p)) * 4);
@@ -404,20 +432,30 @@ k_lnmod_bwd_split(const TA* __restrict__ da, const float* __restrict__ h, const 
           o[0] += pv.x; o[1] += pv.y; o[2] += pv.z; o[3] += pv.w;
         }
         store4(dh + r * W + j, o);
+        if constexpr (GATE) {
+          const float o1[4] = {o[0] * gt[i][0], o[1] * gt[i][1], o[2] * gt[i][2], o[3] * gt[i][3]};
+          const float o2[4] = {o[0] * qn[i][0], o[1] * qn[i][1], o[2] * qn[i][2], o[3] * qn[i][3]};
+          store4(gn.dq + r * W + j, o1);
+          store4(gn.dgate + r * ldmod + j, o2);
+#pragma unroll
+          for (int q = 0; q < 4; ++q) { aq[i][q] += o1[q]; ag[i][q] += o2[q]; }
+        }
       }
     }
   }
   // column sums: the RPB row slots that hold the same columns are combined in shared memory, one reduction per column
   // and block.  which: 0 ln_w, 1 ln_b, 2 shift bias, 3 scale bias
-  for (int which = 0; which < 4; ++which) {
-    float* dst = which == 0 ? dln_w : which == 1 ? dln_b : which == 2 ? dsum : (dsum ? dsum + W : nullptr);
+  for (int which = 0; which < (GATE ? 6 : 4); ++which) {
+    float* dst = which == 0 ? dln_w : which == 1 ? dln_b : which == 2 ? dsum : which == 3 ? (dsum ? dsum + W : nullptr)
+                 : which == 4 ? gn.sum_dq : gn.sum_dgate;
     if (dst == nullptr) continue;  // uniform over the grid
     __syncthreads();
 #pragma unroll
     for (int i = 0; i < NC; ++i)
 #pragma unroll
       for (int q = 0; q < 4; ++q)
-        red[wib][i * 128 + lane * 4 + q] = which == 0 ? aw[i][q] : which == 1 ? ab[i][q] : which == 2 ? as[i][q] : ac[i][q];
+        red[wib][i * 128 + lane * 4 + q] = which == 0 ? aw[i][q] : which == 1 ? ab[i][q] : which == 2 ? as[i][q] : which == 3 ? ac[i][q]
+                                           : which == 4 ? aq[GATE ? i : 0][q] : ag[GATE ? i : 0][q];
     __syncthreads();
     for (int c = threadIdx.x; c < W; c += blockDim.x) {
       // column c = (l + 32 (i P + pp)) 4 + q  ->  chunk = c / 128 = i P + pp, offset in chunk = c % 128

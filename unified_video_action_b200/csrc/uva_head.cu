@@ -243,6 +243,7 @@ struct UvaHead {
   bool fuse_lnpre = false;
   unsigned int* lnpre_bar = nullptr;  // [kLnPrePanels][2] panel barriers of that pre-phase
   bool epi_colsum = true;   // UVA_EPI_COLSUM: bias gradients of mlp.0 / cond_embed reduced in the SiLU' GEMM epilogue (warp shuffles + atomics)
+  bool fuse_gate_ln = true;  // UVA_FUSE_GATE_LN: k_gate_bwd of block b - 1 inside the LayerNorm-modulate backward of block b (78 us instead of 59 + 39)
   bool fuse_colsum = true;  // UVA_FUSE_COLSUM: bias gradients of mlp.2 / gate modulation summed inside k_gate_bwd
   bool final_tc = true;  // UVA_FINAL_TC: final-layer backward (dgrad K = 32, wgrad M = 2C) on the tcgen05 GEMMs
   bool fuse_inproj = true;  // UVA_FUSE_INPROJ: input_proj + first LayerNorm-modulate in one kernel on the latency path
@@ -440,6 +441,7 @@ extern "C" int uva_head_create(const UvaHeadDesc* desc, UvaHead** out) {
   if (const char* e = getenv("UVA_TRAIN_GRAPH")) h->train_graph = atoi(e) != 0;
   if (const char* e = getenv("UVA_TRAIN_GRAPH_ROWS")) h->train_graph_rows = atol(e);
   if (const char* e = getenv("UVA_FUSE_COLSUM")) h->fuse_colsum = atoi(e) != 0;
+  if (const char* e = getenv("UVA_FUSE_GATE_LN")) h->fuse_gate_ln = atoi(e) != 0;
   if (const char* e = getenv("UVA_EPI_COLSUM")) h->epi_colsum = atoi(e) != 0;
   if (const char* e = getenv("UVA_PDL_BIG")) h->pdl_big = atoi(e) != 0;
   if (const char* e = getenv("UVA_PDL_TRAIN")) h->pdl_train = atoi(e) != 0;
